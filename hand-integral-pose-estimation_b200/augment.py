@@ -1,0 +1,39 @@
+"""Drop-in for the hot-path functions of the reference's common/augment.py:
+`compute_similarity_transform` (:18-77) and `get_joint_location_result` (:160-184), running
+on the sm_100a kernels.  The reference's image/patch augmentation code is out of scope."""
+import numpy as np
+import torch
+
+from hipe_b200 import evaluate as _ev
+from nets.loss import FreiHandConfig, softmax_integral_tensor
+
+
+def compute_similarity_transform(X, Y, compute_optimal_scale=False):
+    """augment.py:18-77 for one (J,3) pair, numpy in / numpy out: (d, Z, T, b, c)."""
+    X = np.asarray(X, dtype=np.float64)
+    Y = np.asarray(Y, dtype=np.float64)
+    d, Z, T, b, c = _ev.compute_similarity_transform_batched(X[None], Y[None], compute_optimal_scale)
+    bb = float(b[0].item())
+    return float(d[0].item()), Z[0].cpu().numpy(), T[0].cpu().numpy(), (bb if compute_optimal_scale else 1), \
+        c[0].cpu().numpy()
+
+
+compute_similarity_transform_batched = _ev.compute_similarity_transform_batched
+
+
+def get_joint_location_result(patch_width, patch_height, preds):
+    """augment.py:160-184: soft-argmax, rescale to patch pixels, append a score column of ones.
+    Returns a (B, J, 4) float64 numpy array."""
+    hm_width = preds.shape[-1]
+    hm_height = preds.shape[-2]
+    hm_depth = preds.shape[-3] // FreiHandConfig.num_joints
+    num_joints = preds.shape[1] // hm_depth
+    with torch.no_grad():
+        pred_jts = softmax_integral_tensor(preds, num_joints, hm_width, hm_height, hm_depth)
+    coords = pred_jts.detach().cpu().numpy().astype(float)
+    coords = coords.reshape((coords.shape[0], int(coords.shape[1] / 3), 3))
+    coords[:, :, 0] = (coords[:, :, 0] + 0.5) * patch_width
+    coords[:, :, 1] = (coords[:, :, 1] + 0.5) * patch_height
+    coords[:, :, 2] = coords[:, :, 2] * patch_width
+    scores = np.ones((coords.shape[0], coords.shape[1], 1), dtype=float)
+    return np.concatenate((coords, scores), axis=2)

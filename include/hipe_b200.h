@@ -1,0 +1,167 @@
+/*
+ * hipe_b200.h -- C ABI of libhipe_b200.so: the integral-regression hot path of
+ * mqadri9/hand-integral-pose-estimation as hand-written sm_100a CUDA kernels.
+ *
+ * Conventions:
+ *   - every pointer named *_dev is DEVICE memory owned by the caller; the library allocates
+ *     nothing on those calls, keeps no global mutable state and never synchronises the
+ *     device.  Work is enqueued on `stream` (a cudaStream_t passed as void*) of the CURRENT
+ *     device of the calling thread.  Entry points are re-entrant and thread-safe (the
+ *     reference runs one Python thread per GPU, common/nets/balanced_parallel.py:149-173).
+ *   - the *_host entry points take HOST pointers, allocate/free their own device scratch,
+ *     copy in, compute, copy out and synchronise; they exist for non-PyTorch callers and
+ *     for the end-to-end measurement.
+ *   - return value: 0 = ok; < 0 = argument error (HIPE_E_*); > 0 = a cudaError_t.
+ *   - a heatmap tensor is `n_vol` back-to-back volumes of D*H*W elements, x fastest, which
+ *     is exactly main/model.py:14-20,40-44's contiguous (B, J*D, H, W) output
+ *     (n_vol = B*J, channel = j*D + z).
+ *
+ * Citations are into /root/reference (the replaced Python interface).
+ */
+#ifndef HIPE_B200_H
+#define HIPE_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define HIPE_API __attribute__((visibility("default")))
+#else
+#define HIPE_API
+#endif
+
+/* element types */
+#define HIPE_F32 0
+#define HIPE_BF16 1
+#define HIPE_F64 3
+
+/* argument errors */
+#define HIPE_E_DTYPE (-1)    /* unsupported element type for this argument            */
+#define HIPE_E_SHAPE (-2)    /* non-positive / overflowing dimension                  */
+#define HIPE_E_ALIGN (-3)    /* pointer not aligned to its element size               */
+#define HIPE_E_NULL (-4)     /* required pointer is NULL                              */
+#define HIPE_E_CLUSTER (-5)  /* cluster size not in {0,1,2,4,8}                       */
+#define HIPE_E_ARCH (-6)     /* current device is not compute capability 10.x         */
+
+/* variant selector for the streaming kernels (0 = library default) */
+#define HIPE_VARIANT_AUTO 0
+#define HIPE_VARIANT_TMA 1   /* cp.async.bulk + mbarrier ring through shared memory   */
+#define HIPE_VARIANT_LDG 2   /* 128-bit ld.global.nc straight to registers            */
+
+HIPE_API int hipe_version(void);
+
+/* Short static description of an error code returned by this library. */
+HIPE_API const char* hipe_strerror(int code);
+
+/*
+ * Soft-argmax forward: replaces softmax_integral_tensor (common/nets/loss.py:46-59) and,
+ * with `apply_softmax == 0`, generate_3d_integral_preds_tensor (common/nets/loss.py:23-43)
+ * on already-normalised heatmaps.
+ *   logits_dev : n_vol * D*H*W elements of `dtype` (HIPE_F32 | HIPE_BF16), read-only
+ *   coords_dev : n_vol*3 floats  (x/W-0.5, y/H-0.5, z/D-0.5)  -- loss.py:54-58   (nullable)
+ *   expect_dev : n_vol*3 floats  raw expectations in voxel units -- loss.py:39-41 (nullable)
+ *   stats_dev  : n_vol*2 floats  (max logit, sum exp(logit-max)); input of the backward
+ *                (nullable; written as (0, sum) when apply_softmax == 0)
+ *   cluster    : CTAs cooperating on one volume: 0 = auto, else 1|2|4|8
+ *   variant    : HIPE_VARIANT_*
+ */
+HIPE_API int hipe_softargmax_fwd(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
+                        int apply_softmax, float* coords_dev, float* expect_dev,
+                        float* stats_dev, int cluster, int variant, void* stream);
+
+/*
+ * Soft-argmax backward: what autograd does for loss.backward() through
+ * common/nets/loss.py:46-59 (main/train.py:113), recomputing the softmax from the logits:
+ *   dlogits[i] = p_i * ( gx (x_i - Ex)/W + gy (y_i - Ey)/H + gz (z_i - Ez)/D ) * gscale
+ *   gcoords_dev : n_vol*3 floats, upstream gradient w.r.t. coords
+ *   gscale_dev  : optional device float multiplied into gcoords (NULL = 1)
+ *   dlogits_dev : n_vol * D*H*W elements of `dtype`
+ */
+HIPE_API int hipe_softargmax_bwd(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
+                        const float* stats_dev, const float* expect_dev,
+                        const float* gcoords_dev, const float* gscale_dev, void* dlogits_dev,
+                        int cluster, int variant, void* stream);
+
+/*
+ * Volume softmax: replaces softmax_integral_tensor2 (common/nets/loss.py:61-67); needs the
+ * stats a forward call produced.  probs_dev: n_vol * D*H*W elements of `dtype`.
+ */
+HIPE_API int hipe_volume_softmax(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
+                        const float* stats_dev, void* probs_dev, int cluster, int variant,
+                        void* stream);
+
+/*
+ * L1 integral loss on coordinates: replaces common/nets/loss.py:86-89.
+ *   coords_dev : B*K floats (K = 3*J);  gt_dev, vis_dev : B*K of tgt_dtype (HIPE_F32|HIPE_F64)
+ *   norm       : the value the masked L1 sum is multiplied by (1/B for size_average)
+ *   loss_dev   : one double, sum |c-gt|*vis * norm, accumulated in fp64 in a fixed order
+ *   gcoords_dev: B*K floats, sign(c-gt)*vis*norm  (torch.abs backward is sgn)   (nullable)
+ */
+HIPE_API int hipe_l1_loss_fwd(const float* coords_dev, const void* gt_dev, const void* vis_dev,
+                     int tgt_dtype, long long B, int K, double norm, double* loss_dev,
+                     float* gcoords_dev, void* stream);
+
+/*
+ * Fused JointLocationLoss forward+backward in ONE launch per batch
+ * (common/nets/loss.py:74-91 + main/train.py:113 with upstream gradient 1): every cluster
+ * reduces its volume, forms the three local gradients sign(c-gt)*vis*norm, and streams the
+ * same volume again (from L2 / shared memory) to write dlogits.  Also writes coords,
+ * expect, stats and per-coordinate loss terms; hipe_sum_f64 / hipe_l1_loss_fwd finish the
+ * scalar.  gt/vis are indexed [vol*3 + a], i.e. the (B, 3J) target layout.
+ */
+HIPE_API int hipe_joint_loss_fused(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
+                          const void* gt_dev, const void* vis_dev, int tgt_dtype, double norm,
+                          float* coords_dev, float* expect_dev, float* stats_dev,
+                          double* loss_terms_dev /* n_vol*3 */, void* dlogits_dev,
+                          int cluster, int variant, void* stream);
+
+/*
+ * x[i] *= *gscale_dev for n elements of `dtype`, in place; returns without touching memory when
+ * the scalar is exactly 1.  Used to apply an upstream loss gradient to the dlogits the fused
+ * launch already produced, without a host synchronisation.
+ */
+HIPE_API int hipe_scale_inplace(void* x_dev, int dtype, long long n, const float* gscale_dev, void* stream);
+
+/* Deterministic fp64 sum of n doubles into out_dev[0] (times `scale`). */
+HIPE_API int hipe_sum_f64(const double* in_dev, long long n, double scale, double* out_dev, void* stream);
+
+/*
+ * Batched similarity (Procrustes) alignment: replaces the per-sample loop around
+ * augment.compute_similarity_transform (common/augment.py:18-77, called at
+ * data/FreiHand/FreiHand.py:742) and, with mode == 1, eval.align_w_scale
+ * (main/eval.py:142-165).  All arrays fp64.
+ *   X_dev, Y_dev : N*J*3 targets / inputs
+ *   mode         : 0 = compute_similarity_transform (reflection repaired),
+ *                  1 = align_w_scale (no repair, 1e-8 added to the norms)
+ *   optimal_scale: compute_optimal_scale of augment.py:18 (mode 0 only)
+ *   d N, Z N*J*3, T N*9 (row-major), b N, c N*3      -- each nullable
+ *   pa_dist N*J : ||Z - X||_2 per joint;  raw_dist N*J : ||Y - X||_2 per joint
+ *                 (data/FreiHand/FreiHand.py:766-767,804-807)   -- each nullable
+ */
+HIPE_API int hipe_procrustes_batched(const double* X_dev, const double* Y_dev, long long N, int J,
+                            int mode, int optimal_scale, double* d_dev, double* Z_dev,
+                            double* T_dev, double* b_dev, double* c_dev, double* pa_dist_dev,
+                            double* raw_dist_dev, void* stream);
+
+/*
+ * Host-buffer convenience entry points (synchronous).
+ * hipe_joint_location_loss_host: JointLocationLoss forward (+ backward when dlogits_host is
+ * non-NULL) on host logits, streamed to the current device in chunks of `chunk_samples`
+ * samples (0 = auto) with copies overlapped against the kernels.
+ *   logits_host : B * J * D*H*W elements (pinned memory recommended)
+ *   gt/vis_host : B * 3J of tgt_dtype
+ *   loss_host   : one double;  coords_host : B*3J floats (nullable)
+ */
+HIPE_API int hipe_joint_location_loss_host(const void* logits_host, int dtype, long long B, int J, int D,
+                                  int H, int W, const void* gt_host, const void* vis_host,
+                                  int tgt_dtype, int size_average, double* loss_host,
+                                  float* coords_host, void* dlogits_host, long long chunk_samples);
+
+HIPE_API int hipe_procrustes_host(const double* X_host, const double* Y_host, long long N, int J, int mode,
+                         int optimal_scale, double* Z_host, double* pa_mpjpe, double* mpjpe);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HIPE_B200_H */

@@ -1,0 +1,58 @@
+"""Seeded synthetic inputs shared by tests, smoke() and bench.py."""
+import numpy as np
+
+REGIMES = {"noise": (0.0, 2.0), "peaked": (12.0, 2.0), "sharp": (20.0, 1.5)}
+
+
+def heatmaps(B, J, D, H, W, regime="peaked", seed=0, dtype=np.float32):
+    """(B, J*D, H, W) logits = A*exp(-|v-c|^2/(2 s^2)) + N(0,1), centre c uniform per volume."""
+    A, sig = REGIMES[regime]
+    rng = np.random.default_rng(seed)
+    out = rng.standard_normal((B, J, D, H, W)).astype(np.float32)
+    if A != 0.0:
+        c = rng.uniform(0, 1, size=(B, J, 3)) * np.array([W - 1, H - 1, D - 1])
+        z = np.arange(D, dtype=np.float32)[None, None, :, None, None]
+        y = np.arange(H, dtype=np.float32)[None, None, None, :, None]
+        x = np.arange(W, dtype=np.float32)[None, None, None, None, :]
+        cx = c[..., 0].astype(np.float32)[:, :, None, None, None]
+        cy = c[..., 1].astype(np.float32)[:, :, None, None, None]
+        cz = c[..., 2].astype(np.float32)[:, :, None, None, None]
+        r2 = (x - cx) ** 2 + (y - cy) ** 2 + (z - cz) ** 2
+        out += (A * np.exp(-r2 / (2 * sig * sig))).astype(np.float32)
+    return out.reshape(B, J * D, H, W).astype(dtype)
+
+
+def targets(B, J, seed=0, zero_vis_frac=0.0):
+    rng = np.random.default_rng(seed + 7919)
+    gt = rng.uniform(-0.5, 0.5, size=(B, 3 * J))
+    vis = np.ones((B, 3 * J))
+    if zero_vis_frac > 0:
+        vis[rng.uniform(size=vis.shape) < zero_vis_frac] = 0.0
+    return gt, vis
+
+
+def random_rotations(n, rng):
+    q, r = np.linalg.qr(rng.standard_normal((n, 3, 3)))
+    q = q * np.sign(np.diagonal(r, axis1=1, axis2=2))[:, None, :]
+    q[:, :, 0] *= np.sign(np.linalg.det(q))[:, None]
+    return q
+
+
+def hand_like_joints(n, J=21, seed=0):
+    """Synthetic hand-sized joint sets in metres (the reference's own arrays are not shipped to
+    the GPU box): an anisotropic blob ~ 8 cm across, 0.5-1 m from the camera."""
+    rng = np.random.default_rng(seed)
+    base = rng.standard_normal((n, J, 3)) * np.array([0.035, 0.03, 0.015])
+    return base + rng.uniform([-0.1, -0.1, 0.5], [0.1, 0.1, 1.0], size=(n, 1, 3))
+
+
+def procrustes_pairs(n, J=21, seed=0, noise=0.005, mirror_frac=0.0):
+    """(X, Y): X = 1.1 * Y R + 0.3 + N(0, noise); a fraction of X mirrored."""
+    rng = np.random.default_rng(seed)
+    Y = hand_like_joints(n, J, seed + 1)
+    R = random_rotations(n, rng)
+    X = 1.1 * np.einsum("njk,nkl->njl", Y, R) + 0.3 + rng.standard_normal((n, J, 3)) * noise
+    if mirror_frac > 0:
+        m = rng.uniform(size=n) < mirror_frac
+        X[m, :, 0] *= -1.0
+    return X, Y
