@@ -51,7 +51,8 @@ extern "C" int hipe_joint_location_loss_host(const void* logits_host, int dtype,
                                              int D, int H, int W, const void* gt_host,
                                              const void* vis_host, int tgt_dtype, int size_average,
                                              double* loss_host, float* coords_host,
-                                             void* dlogits_host, long long chunk_samples) {
+                                             void* dlogits_host, void* dlogits_dev,
+                                             long long chunk_samples) {
     if (!logits_host || !gt_host || !vis_host || !loss_host) return HIPE_E_NULL;
     if (dtype != HIPE_F32 && dtype != HIPE_BF16) return HIPE_E_DTYPE;
     if (tgt_dtype != HIPE_F32 && tgt_dtype != HIPE_F64) return HIPE_E_DTYPE;
@@ -67,7 +68,10 @@ extern "C" int hipe_joint_location_loss_host(const void* logits_host, int dtype,
     }
     if (chunk_samples > B) chunk_samples = B;
     const double norm = size_average ? 1.0 / (double)B : 1.0;
-    const bool want_grad = dlogits_host != nullptr;
+    const bool to_host = dlogits_host != nullptr;
+    const bool want_grad = to_host || dlogits_dev != nullptr;
+    // with a caller-owned device gradient buffer the backward writes straight into it
+    const bool stage_grad = to_host && dlogits_dev == nullptr;
     constexpr int NBUF = 3;
 
     int rc = 0;
@@ -89,7 +93,7 @@ extern "C" int hipe_joint_location_loss_host(const void* logits_host, int dtype,
         HIPE_CK(cudaEventCreateWithFlags(&ev_cmp[i], cudaEventDisableTiming));
         HIPE_CK(cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming));
         HIPE_CK(cudaMallocAsync((void**)&d_logits[i], chunk_samples * sample_bytes, s_cmp));
-        if (want_grad) HIPE_CK(cudaMallocAsync((void**)&d_grad[i], chunk_samples * sample_bytes, s_cmp));
+        if (stage_grad) HIPE_CK(cudaMallocAsync((void**)&d_grad[i], chunk_samples * sample_bytes, s_cmp));
     }
     HIPE_CK(cudaMallocAsync((void**)&d_gt, B * K * tsz, s_cmp));
     HIPE_CK(cudaMallocAsync((void**)&d_vis, B * K * tsz, s_cmp));
@@ -113,7 +117,7 @@ extern "C" int hipe_joint_location_loss_host(const void* logits_host, int dtype,
         // the buffer pair is free once chunk c-NBUF has been computed (and copied out)
         if (c >= NBUF) {
             HIPE_CK(cudaStreamWaitEvent(s_in, ev_cmp[bi], 0));
-            if (want_grad) HIPE_CK(cudaStreamWaitEvent(s_cmp, ev_out[bi], 0));
+            if (stage_grad) HIPE_CK(cudaStreamWaitEvent(s_cmp, ev_out[bi], 0));
         }
         HIPE_CK(cudaMemcpyAsync(d_logits[bi], (const unsigned char*)logits_host + b0 * sample_bytes,
                                 nb * sample_bytes, cudaMemcpyHostToDevice, s_in));
@@ -121,16 +125,18 @@ extern "C" int hipe_joint_location_loss_host(const void* logits_host, int dtype,
         HIPE_CK(cudaStreamWaitEvent(s_cmp, ev_in[bi], 0));
         HIPE_RC(hipe_softargmax_fwd(d_logits[bi], dtype, n_vol, D, H, W, 1, d_coords + b0 * K,
                                     d_expect + b0 * K, d_stats + b0 * J * 2, 0, 0, s_cmp));
+        unsigned char* grad_dst = stage_grad ? d_grad[bi]
+                                             : (unsigned char*)dlogits_dev + b0 * sample_bytes;
         if (want_grad) {
             HIPE_RC(hipe_l1_loss_fwd(d_coords + b0 * K, d_gt + b0 * K * tsz, d_vis + b0 * K * tsz,
                                      tgt_dtype, nb, K, norm, d_loss + 1, d_g + b0 * K, s_cmp));
             HIPE_RC(hipe_softargmax_bwd(d_logits[bi], dtype, n_vol, D, H, W, d_stats + b0 * J * 2,
-                                        d_expect + b0 * K, d_g + b0 * K, nullptr, d_grad[bi], 0, 0, s_cmp));
+                                        d_expect + b0 * K, d_g + b0 * K, nullptr, grad_dst, 0, 0, s_cmp));
         }
         HIPE_CK(cudaEventRecord(ev_cmp[bi], s_cmp));
-        if (want_grad) {
+        if (to_host) {
             HIPE_CK(cudaStreamWaitEvent(s_out, ev_cmp[bi], 0));
-            HIPE_CK(cudaMemcpyAsync((unsigned char*)dlogits_host + b0 * sample_bytes, d_grad[bi],
+            HIPE_CK(cudaMemcpyAsync((unsigned char*)dlogits_host + b0 * sample_bytes, grad_dst,
                                     nb * sample_bytes, cudaMemcpyDeviceToHost, s_out));
             HIPE_CK(cudaEventRecord(ev_out[bi], s_out));
         }

@@ -28,7 +28,7 @@ SIGNATURES = {
     "hipe_sum_f64": (_i, [_vp, _ll, _d, _vp, _vp]),
     "hipe_procrustes_batched": (_i, [_vp, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hipe_joint_location_loss_host": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp,
-                                           _ll]),
+                                           _vp, _ll]),
     "hipe_procrustes_host": (_i, [_vp, _vp, _ll, _i, _i, _i, _vp, _vp, _vp]),
 }
 

@@ -18,6 +18,33 @@ DEFAULT_CLUSTER = 0
 DEFAULT_VARIANT = 0
 
 
+# bench.py's accounting: kernels launched through this module, and (when a dict is installed)
+# CUDA-event pairs recorded on the launching stream around each named launch.
+LAUNCHES = 0
+KERNEL_EVENTS = None
+
+
+class _launch:
+    """Counts one kernel launch; with KERNEL_EVENTS set, brackets it with events on `stream`."""
+
+    def __init__(self, name, tensor):
+        self.name, self.tensor = name, tensor
+
+    def __enter__(self):
+        global LAUNCHES
+        LAUNCHES += 1
+        if KERNEL_EVENTS is not None:
+            self.ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            self.ev[0].record(torch.cuda.current_stream(self.tensor.device))
+        return self
+
+    def __exit__(self, *exc):
+        if KERNEL_EVENTS is not None and exc[0] is None:
+            self.ev[1].record(torch.cuda.current_stream(self.tensor.device))
+            KERNEL_EVENTS.setdefault(self.name, []).append(self.ev)
+        return False
+
+
 def _need_cuda(t, name):
     if not isinstance(t, torch.Tensor):
         raise TypeError("%s must be a torch.Tensor, got %s" % (name, type(t).__name__))
@@ -52,7 +79,7 @@ def softargmax_forward(logits, n_vol, D, H, W, apply_softmax=True, cluster=None,
     coords = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
     expect = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
     stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
+    with torch.cuda.device(dev), _launch("softargmax_fwd", logits):
         check(_lib.load().hipe_softargmax_fwd(
             logits.data_ptr(), code, n_vol, D, H, W, 1 if apply_softmax else 0,
             coords.data_ptr(), expect.data_ptr(), stats.data_ptr(),
@@ -72,7 +99,7 @@ def softargmax_backward(logits, n_vol, D, H, W, stats, expect, gcoords, gscale=N
     if gscale is not None:
         gscale = gscale.to(device=logits.device, dtype=torch.float32).reshape(1).contiguous()
     out = torch.empty_like(logits)
-    with torch.cuda.device(logits.device):
+    with torch.cuda.device(logits.device), _launch("softargmax_bwd", logits):
         check(_lib.load().hipe_softargmax_bwd(
             logits.data_ptr(), code, n_vol, D, H, W, stats.data_ptr(), expect.data_ptr(),
             gcoords.data_ptr(), _ptr(gscale), out.data_ptr(),
@@ -90,7 +117,7 @@ def volume_softmax(logits, n_vol, D, H, W, stats=None, cluster=None, variant=Non
     if stats is None:
         _, _, stats = softargmax_forward(logits, n_vol, D, H, W, True, cluster, variant)
     out = torch.empty_like(logits)
-    with torch.cuda.device(logits.device):
+    with torch.cuda.device(logits.device), _launch("volume_softmax", logits):
         check(_lib.load().hipe_volume_softmax(
             logits.data_ptr(), code, n_vol, D, H, W, stats.data_ptr(), out.data_ptr(),
             DEFAULT_CLUSTER if cluster is None else cluster,
@@ -118,7 +145,7 @@ def l1_loss(coords, gt, vis, norm, want_grad=True):
     B, K = coords.shape
     loss = torch.empty((), dtype=torch.float64, device=coords.device)
     g = torch.empty_like(coords) if want_grad else None
-    with torch.cuda.device(coords.device):
+    with torch.cuda.device(coords.device), _launch("l1_loss", coords):
         check(_lib.load().hipe_l1_loss_fwd(coords.data_ptr(), gt.data_ptr(), vis.data_ptr(), code, B, K,
                                            float(norm), loss.data_ptr(), _ptr(g), _stream(coords)))
     return loss, g
@@ -128,7 +155,7 @@ def sum_f64(x, scale=1.0):
     _need_cuda(x, "x")
     x = x.to(torch.float64).contiguous()
     out = torch.empty((), dtype=torch.float64, device=x.device)
-    with torch.cuda.device(x.device):
+    with torch.cuda.device(x.device), _launch("sum_f64", x):
         check(_lib.load().hipe_sum_f64(x.data_ptr(), x.numel(), float(scale), out.data_ptr(), _stream(x)))
     return out
 
@@ -148,7 +175,7 @@ def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, varian
     stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
     terms = torch.empty((n_vol * 3,), dtype=torch.float64, device=dev)
     dlogits = torch.empty_like(logits)
-    with torch.cuda.device(dev):
+    with torch.cuda.device(dev), _launch("joint_loss_fused", logits):
         check(_lib.load().hipe_joint_loss_fused(
             logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
             coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), dlogits.data_ptr(),
@@ -171,7 +198,7 @@ def procrustes(X, Y, mode=0, optimal_scale=True, want=("Z", "pa_dist", "raw_dist
     shapes = {"d": (N,), "Z": (N, J, 3), "T": (N, 3, 3), "b": (N,), "c": (N, 3), "pa_dist": (N, J),
               "raw_dist": (N, J)}
     out = {k: torch.empty(shapes[k], dtype=torch.float64, device=X.device) for k in want}
-    with torch.cuda.device(X.device):
+    with torch.cuda.device(X.device), _launch("procrustes", X):
         check(_lib.load().hipe_procrustes_batched(
             X.data_ptr(), Y.data_ptr(), N, J, int(mode), 1 if optimal_scale else 0,
             _ptr(out.get("d")), _ptr(out.get("Z")), _ptr(out.get("T")), _ptr(out.get("b")),
@@ -246,7 +273,7 @@ class FusedJointLossFunction(torch.autograd.Function):
         (dlogits,) = ctx.saved_tensors
         # in place, on device, no host sync; the kernel returns at once when the scalar is 1
         gs = grad_loss.to(device=dlogits.device, dtype=torch.float32).reshape(1).contiguous()
-        with torch.cuda.device(dlogits.device):
+        with torch.cuda.device(dlogits.device), _launch("scale_inplace", dlogits):
             check(_lib.load().hipe_scale_inplace(dlogits.data_ptr(), _logits_code(dlogits), dlogits.numel(),
                                                  gs.data_ptr(), _stream(dlogits)))
         return dlogits.view(ctx.in_shape), None, None, None, None, None, None, None

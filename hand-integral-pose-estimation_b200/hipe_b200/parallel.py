@@ -1,0 +1,154 @@
+"""Batch-sharded form of the path: one process per GPU (torchrun), `torch.distributed` for the
+plumbing.  Replaces the reference's single-process DataParallelCriterion + Reduce
+(common/nets/balanced_parallel.py:97-127,46-55) and the eval scripts' gather of whole heatmaps to
+GPU 0 (main/evaluate.py:62-63, main/test.py:91-92).
+
+Every (sample, joint) volume and every Procrustes sample is independent, so rank r keeps the
+samples `shard_bounds(B, world, r)` -- the dim-0 chunking `scatter` does
+(balanced_parallel.py:122) -- and no volume, probability or heatmap gradient ever crosses a GPU.
+The only exchange is ONE all-gather per step of a packed record per rank,
+
+    [ sum_r |c - gt| * vis ,  B_r ,  coords_r (B_max * 3J, zero padded) ]      (fp64)
+
+after which every rank holds all predicted joints and combines the per-replica losses in fixed
+rank order (bit-identical on every rank).  Backward needs no collective: each rank scales its own
+gradient by 1/world, exactly what `Reduce.backward` broadcasts (balanced_parallel.py:52-55).
+"""
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+
+def shard_bounds(n, world, rank):
+    """[lo, hi) of rank's rows when n rows are split like torch.chunk / scatter: ceil(n/world) per
+    rank, the tail ranks short or empty."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("bad rank %d of world %d" % (rank, world))
+    per = -(-n // world)
+    lo = min(rank * per, n)
+    return lo, min(lo + per, n)
+
+
+def max_shard(n, world):
+    return -(-n // world)
+
+
+def pack_record(loss_sum, coords, b_max):
+    """-> 1-D fp64 tensor [loss_sum, B_local, coords padded to b_max rows]."""
+    b, k = coords.shape
+    rec = torch.zeros(2 + b_max * k, dtype=torch.float64, device=coords.device)
+    rec[0] = loss_sum.to(torch.float64)
+    rec[1] = float(b)
+    rec[2:2 + b * k] = coords.reshape(-1).to(torch.float64)
+    return rec
+
+
+def unpack_records(recs, k, counts=None):
+    """list of per-rank records -> (loss_sums (world,), counts list[int], coords (B_global, k) fp64).
+    `counts` known a priori (from `shard_bounds`) avoids reading them back from the device."""
+    sums = torch.stack([r[0] for r in recs])
+    if counts is None:
+        counts = [int(round(float(r[1]))) for r in recs]
+    rows = [r[2:2 + c * k].reshape(c, k) for r, c in zip(recs, counts)]
+    return sums, counts, torch.cat(rows, dim=0)
+
+
+def gather_records(rec, group=None):
+    world = dist.get_world_size(group)
+    out = [torch.empty_like(rec) for _ in range(world)]
+    dist.all_gather(out, rec, group=group)
+    return out
+
+
+def combine_replica_losses(sums, counts, size_average=True):
+    """What DataParallelCriterion returns (balanced_parallel.py:127): the mean over replicas of
+    each replica's `sum / len(coord_out)` (loss.py:88-89); summed in rank order.  Replicas with an
+    empty shard do not exist in the reference (scatter yields fewer chunks) and are skipped."""
+    total = torch.zeros((), dtype=torch.float64, device=sums.device)
+    live = 0
+    for s, c in zip(sums, counts):
+        if c == 0:
+            continue
+        total = total + (s / c if size_average else s)
+        live += 1
+    return total / max(live, 1), live
+
+
+def _local_cuda_loss(heatmap_out, gt_coord, gt_vis):
+    """(loss_sum_local [differentiable, fp64], coords (B_local, 3J) fp32) on this rank's GPU."""
+    from nets.loss import FreiHandConfig, softmax_integral_tensor
+    from . import ops
+    joint_num = int(gt_coord.shape[1] / 3)
+    w, h = heatmap_out.shape[-1], heatmap_out.shape[-2]
+    d = heatmap_out.shape[-3] // FreiHandConfig.num_joints
+    coords = softmax_integral_tensor(heatmap_out, joint_num, w, h, d)
+    loss_sum = ops.IntegralL1Function.apply(coords, gt_coord.to(torch.float64), gt_vis.to(torch.float64), 1.0)
+    return loss_sum, coords
+
+
+class ShardedJointLocationLoss(nn.Module):
+    """JointLocationLoss over a batch sharded across the ranks of `group`.
+
+        crit = ShardedJointLocationLoss()
+        loss = crit(heatmap_local, gt_local, vis_local)     # same value on every rank
+        loss.backward()                                      # local kernels only
+        crit.coords                                          # (B_global, 3J) on every rank
+
+    `local_fn(heatmap, gt, vis) -> (loss_sum, coords)` is the per-rank computation; the default
+    runs the sm_100a kernels.  (The CPU tests inject an oracle-backed function to exercise the
+    exchange logic over gloo.)"""
+
+    def __init__(self, group=None, local_fn=None, global_batch=None):
+        """`global_batch`: total rows over all ranks, when every rank holds its `shard_bounds`
+        share; the exchange then needs no size negotiation and no host synchronisation."""
+        super().__init__()
+        self.size_average = True
+        self.group = group
+        self.local_fn = local_fn or _local_cuda_loss
+        self.global_batch = global_batch
+        self.coords = None
+
+    def forward(self, heatmap_out, gt_coord, gt_vis):
+        world = dist.get_world_size(self.group)
+        loss_sum, coords = self.local_fn(heatmap_out, gt_coord, gt_vis)
+        b_local, k = coords.shape
+        counts = None
+        if self.global_batch is not None:
+            counts = [hi - lo for lo, hi in (shard_bounds(self.global_batch, world, r) for r in range(world))]
+            if counts[dist.get_rank(self.group)] != b_local:
+                raise ValueError("this rank holds %d rows, shard_bounds(%d, %d) gives it %d"
+                                 % (b_local, self.global_batch, world, counts[dist.get_rank(self.group)]))
+            b_max = max_shard(self.global_batch, world)
+        else:
+            # one extra tiny collective only when the caller did not promise the shard sizes
+            t = torch.tensor([b_local], dtype=torch.int64, device=coords.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+            b_max = int(t.item())
+        with torch.no_grad():
+            recs = gather_records(pack_record(loss_sum.detach(), coords.detach(), b_max), self.group)
+            sums, counts, allc = unpack_records(recs, k, counts)
+            value, live = combine_replica_losses(sums, counts, self.size_average)
+        self.coords = allc.to(coords.dtype)
+        if b_local == 0:
+            return value
+        # value of the global loss, gradient of this replica's share (1/live of its own loss)
+        own = loss_sum / b_local if self.size_average else loss_sum
+        return value + (own - own.detach()) / live
+
+
+def sharded_pa_mpjpe(gt_local, pred_local, group=None, mode=0):
+    """(PA-MPJPE, MPJPE) over all ranks' samples (data/FreiHand/FreiHand.py:742,766-767,804-807):
+    local batched Procrustes, then one all-gather of [sum_pa, sum_raw, n_local*J]."""
+    from . import evaluate, ops
+    X, Y = evaluate._as_cuda64(gt_local), evaluate._as_cuda64(pred_local)
+    o = ops.procrustes(X, Y, mode, True, want=("pa_dist", "raw_dist"))
+    rec = torch.stack([ops.sum_f64(o["pa_dist"]), ops.sum_f64(o["raw_dist"]),
+                       torch.tensor(float(o["pa_dist"].numel()), dtype=torch.float64, device=X.device)])
+    return reduce_error_sums(gather_records(rec, group))
+
+
+def reduce_error_sums(recs):
+    tot = torch.zeros(3, dtype=torch.float64, device=recs[0].device)
+    for r in recs:                      # fixed rank order
+        tot = tot + r
+    return tot[0] / tot[2], tot[1] / tot[2]

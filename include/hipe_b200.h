@@ -146,17 +146,21 @@ HIPE_API int hipe_procrustes_batched(const double* X_dev, const double* Y_dev, l
 
 /*
  * Host-buffer convenience entry points (synchronous).
- * hipe_joint_location_loss_host: JointLocationLoss forward (+ backward when dlogits_host is
- * non-NULL) on host logits, streamed to the current device in chunks of `chunk_samples`
- * samples (0 = auto) with copies overlapped against the kernels.
+ * hipe_joint_location_loss_host: JointLocationLoss forward (+ backward when dlogits_host or
+ * dlogits_dev is non-NULL) on host logits, streamed to the current device in chunks of
+ * `chunk_samples` samples (0 = auto) with copies overlapped against the kernels.
  *   logits_host : B * J * D*H*W elements (pinned memory recommended)
  *   gt/vis_host : B * 3J of tgt_dtype
  *   loss_host   : one double;  coords_host : B*3J floats (nullable)
+ *   dlogits_host: gradient copied back to the host (nullable)
+ *   dlogits_dev : caller-owned DEVICE buffer of B * J * D*H*W elements that receives the
+ *                 gradient where the next consumer (the head's backward) wants it (nullable)
  */
 HIPE_API int hipe_joint_location_loss_host(const void* logits_host, int dtype, long long B, int J, int D,
                                   int H, int W, const void* gt_host, const void* vis_host,
                                   int tgt_dtype, int size_average, double* loss_host,
-                                  float* coords_host, void* dlogits_host, long long chunk_samples);
+                                  float* coords_host, void* dlogits_host, void* dlogits_dev,
+                                  long long chunk_samples);
 
 HIPE_API int hipe_procrustes_host(const double* X_host, const double* Y_host, long long N, int J, int mode,
                          int optimal_scale, double* Z_host, double* pa_mpjpe, double* mpjpe);

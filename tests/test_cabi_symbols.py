@@ -1,0 +1,69 @@
+"""CPU: the C-ABI shared library builds for sm_100a, loads without a GPU, and exports exactly the
+entry points include/hipe_b200.h declares; the ctypes table mirrors the header."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "hipe_b200.h")
+
+
+def declared():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return re.findall(r"HIPE_API\s+[\w\s\*]+?\b(hipe_\w+)\s*\(", src)
+
+
+def test_header_declares_the_path():
+    names = declared()
+    for need in ("hipe_softargmax_fwd", "hipe_softargmax_bwd", "hipe_l1_loss_fwd", "hipe_joint_loss_fused",
+                 "hipe_volume_softmax", "hipe_procrustes_batched", "hipe_joint_location_loss_host",
+                 "hipe_procrustes_host", "hipe_version", "hipe_strerror"):
+        assert need in names
+
+
+def test_library_exports_every_declared_symbol():
+    from hipe_b200 import _build, _lib
+    path = _build.build()
+    lib = ctypes.CDLL(path)
+    for name in declared():
+        assert hasattr(lib, name), "libhipe_b200.so does not export %s" % name
+    assert sorted(_lib.SIGNATURES) == sorted(declared())
+    assert _lib.load().hipe_version() >= 100
+    assert _lib.load().hipe_strerror(-5).decode().startswith("cluster")
+
+
+def test_library_is_sm100a_only_and_uses_bulk_copies():
+    from hipe_b200 import _build
+    path = _build.build()
+    out = subprocess.run(["cuobjdump", "-lelf", path], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    archs = set(re.findall(r"sm_\d+a?", out.stdout))
+    assert archs == {"sm_100a"}, archs
+    sass = subprocess.run(["cuobjdump", "-sass", path], capture_output=True, text=True).stdout
+    assert "UBLKCP" in sass            # cp.async.bulk (TMA 1-D) in the streaming kernels
+    assert "MUFU.EX2" in sass
+
+
+def test_no_cpu_path():
+    import torch
+    from hipe_b200 import ops
+    from nets import loss as L
+    x = torch.zeros(1, 21 * 4, 4, 4)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        ops.softargmax_forward(x, 21, 4, 4, 4)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        L.JointLocationLoss()(x, torch.zeros(1, 63), torch.ones(1, 63))
+
+
+def test_product_does_not_import_the_oracle():
+    pkg = os.path.join(ROOT, "hand-integral-pose-estimation_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f

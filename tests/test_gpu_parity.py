@@ -245,7 +245,7 @@ def test_host_entry_points():
     coords = np.empty((B, 3 * J), np.float32)
     dl = np.empty_like(hm)
     rc = lib.hipe_joint_location_loss_host(hm.ctypes.data, _lib.F32, B, J, D, H, W, gt.ctypes.data, vis.ctypes.data,
-                                           _lib.F64, 1, ctypes.byref(loss), coords.ctypes.data, dl.ctypes.data, 2)
+                                           _lib.F64, 1, ctypes.byref(loss), coords.ctypes.data, dl.ctypes.data, None, 2)
     assert rc == 0
     ref_loss, ref_c = O.joint_location_loss(hm.astype(np.float64), gt, vis, return_coords=True)
     assert abs(loss.value - ref_loss) <= 1e-5 * ref_loss
