@@ -128,6 +128,13 @@ __device__ __forceinline__ float dsmem_ld_f32(uint32_t local_saddr, uint32_t ran
     asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
     return v;
 }
+__device__ __forceinline__ double dsmem_ld_f64(uint32_t local_saddr, uint32_t rank) {
+    uint32_t remote;
+    double v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_saddr), "r"(rank));
+    asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(v) : "r"(remote) : "memory");
+    return v;
+}
 __device__ __forceinline__ void dsmem_st_f32(uint32_t local_saddr, uint32_t rank, float v) {
     uint32_t remote;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_saddr), "r"(rank));

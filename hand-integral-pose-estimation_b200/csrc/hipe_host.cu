@@ -80,8 +80,8 @@ extern "C" int hipe_joint_location_loss_host(const void* logits_host, int dtype,
     unsigned char* d_logits[NBUF] = {};
     unsigned char* d_grad[NBUF] = {};
     unsigned char *d_gt = nullptr, *d_vis = nullptr;
-    float *d_coords = nullptr, *d_expect = nullptr, *d_stats = nullptr, *d_g = nullptr;
-    double* d_loss = nullptr;
+    float *d_coords = nullptr, *d_stats = nullptr, *d_g = nullptr;
+    double *d_expect = nullptr, *d_loss = nullptr;
     const long long nchunks = (B + chunk_samples - 1) / chunk_samples;
 
     keep_pool_memory();
@@ -98,7 +98,7 @@ extern "C" int hipe_joint_location_loss_host(const void* logits_host, int dtype,
     HIPE_CK(cudaMallocAsync((void**)&d_gt, B * K * tsz, s_cmp));
     HIPE_CK(cudaMallocAsync((void**)&d_vis, B * K * tsz, s_cmp));
     HIPE_CK(cudaMallocAsync((void**)&d_coords, B * K * sizeof(float), s_cmp));
-    HIPE_CK(cudaMallocAsync((void**)&d_expect, B * K * sizeof(float), s_cmp));
+    HIPE_CK(cudaMallocAsync((void**)&d_expect, B * K * sizeof(double), s_cmp));
     HIPE_CK(cudaMallocAsync((void**)&d_stats, B * J * 2 * sizeof(float), s_cmp));
     HIPE_CK(cudaMallocAsync((void**)&d_g, B * K * sizeof(float), s_cmp));
     HIPE_CK(cudaMallocAsync((void**)&d_loss, 2 * sizeof(double), s_cmp));
@@ -158,7 +158,7 @@ done:
             if (d_logits[i]) cudaFreeAsync(d_logits[i], s_cmp);
             if (d_grad[i]) cudaFreeAsync(d_grad[i], s_cmp);
         }
-        void* small[] = {d_gt, d_vis, d_coords, d_expect, d_stats, d_g, d_loss};
+        void* small[] = {d_gt, d_vis, d_coords, (void*)d_expect, d_stats, d_g, d_loss};
         for (void* q : small)
             if (q) cudaFreeAsync(q, s_cmp);
         cudaStreamSynchronize(s_cmp);

@@ -16,11 +16,21 @@
 // a producer warp with 1-D TMA bulk copies completing on mbarriers (HIPE_VARIANT_TMA), or by
 // 128-bit ld.global.nc straight into registers (HIPE_VARIANT_LDG).
 //
-// Softmax is "online": each thread keeps a private running max m and rescales its six
-// accumulators when a stage raises it; (m, l, Sx, Sy, Sz) partials are merged thread ->
+// Softmax is "online": each thread keeps a private running max m and rescales its four
+// accumulators when a stage raises it; (m, S0, Sx, Sy, Sz) partials are merged thread ->
 // warp (shuffles) -> CTA (shared memory) -> cluster (DSMEM).  The backward recomputes
 // p_i = exp(s_i - M)/L from the logits and the saved (M, L): probabilities never exist in
 // HBM.
+//
+// Precision.  The gradient is p_i * sum_a g_a (idx_a - E_a)/dim_a, so an absolute error in
+// an expectation E_a is amplified by 1/|idx_a - E_a| at exactly the voxels that carry the
+// largest gradient (a sharp peak sits within a fraction of a voxel of E).  fp32 sums of
+// e*idx and e drift apart by ~1e-6 relative = 3e-5 voxels, which alone breaks a 1e-5 gate.
+// So: exponentials are fp32 (MUFU.EX2), but every 16-byte vector's (sum e, sum j*e) is
+// widened once and the four moment sums are carried in fp64 -- all of them built from the
+// SAME rounded row sums, so rounding errors only re-weight voxels (an error ~ eps*sigma, not
+// eps*E) -- and the expectations travel to the backward as fp64, where they are split into
+// hi+lo floats so that (idx - E) keeps its absolute accuracy in fp32 arithmetic.
 #include "hipe_common.cuh"
 #include <stdlib.h>
 
@@ -53,11 +63,11 @@ struct Params {
     int pol1, pol2;  // L2 policy of the TMA loads of pass 1 / pass 2: 0 normal, 1 evict_first, 2 evict_last
     // reduce outputs
     float* coords;
-    float* expect;
+    double* expect;
     float* stats;
     // write inputs
     const float* stats_in;
-    const float* expect_in;
+    const double* expect_in;
     const float* gcoords;
     const float* gscale;
     // fused
@@ -72,31 +82,47 @@ struct SmemLayout {
     // dynamic shared memory: [stages][kStageBytes] then this struct
     unsigned long long full[kStages];
     unsigned long long empty[kStages];
-    float wred[kConsumers / 32][5];
-    float part[5];                 // this CTA's partial, read by cluster peers through DSMEM
-    float all[kMaxCluster][5];
-    float fin[8];                  // M, L, Ex, Ey, Ez, gx, gy, gz
+    double wred[kConsumers / 32][4];
+    float wmax[kConsumers / 32];
+    double part[4];                // this CTA's partial (S0, Sx, Sy, Sz), read by peers through DSMEM
+    float part_m;                  // ... and the maximum it is relative to
+    double all[kMaxCluster][4];
+    float all_m[kMaxCluster];
+    double finE[3];                // Ex, Ey, Ez (voxel units)
+    float fin[5];                  // M, L, gx, gy, gz
 };
 
 __device__ __forceinline__ void consumer_barrier() {
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
 }
 
-template <bool kSoftmax, int VEC>
+template <bool kSoftmax>
 struct Acc {
-    float m;        // running max (natural units)
-    float mL;       // fl(m * log2e)
-    float cx[VEC];  // per-column sums of e
-    float sy, sz;
+    float m;    // running max (natural units)
+    float mL;   // fl(m * log2e): the exponent offset every e of this thread is relative to
+    double s0;  // sum e
+    double sx;  // sum e * (x - x0)   (x0 = the thread's first column)
+    double sy;  // sum e * y
+    double sz;  // sum e * z
     __device__ __forceinline__ void init() {
         m = kSoftmax ? kNegInf : 0.f;
         mL = kSoftmax ? kNegInf : 0.f;
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) cx[j] = 0.f;
-        sy = 0.f;
-        sz = 0.f;
+        s0 = sx = sy = sz = 0.0;
+    }
+    __device__ __forceinline__ void scale(float f) {
+        const double d = (double)f;
+        s0 *= d; sx *= d; sy *= d; sz *= d;
     }
 };
+
+// Weight that re-bases a partial computed against maximum m_from onto maximum m_to >= m_from.
+// Every exponential is 2^(s*log2e - fl(m*log2e)), so the weight is 2^(fl(m_from*log2e) -
+// fl(m_to*log2e)) with the SAME rounded products (no contraction): a partial is re-based by
+// exactly the offset its exponentials were computed against.
+__device__ __forceinline__ float rebase_weight(float m_from, float m_to) {
+    return (m_from == kNegInf) ? 0.f
+                               : ex2(__fsub_rn(__fmul_rn(m_from, kLog2e), __fmul_rn(m_to, kLog2e)));
+}
 
 template <typename T, bool kTma, int kOp>
 __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
@@ -183,21 +209,22 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
     const int rr = active ? tid / p.G : 0;
     // number of row visits of this thread inside the CTA's range
     const int nvis = (active && nrows > rr) ? (nrows - rr + p.R - 1) / p.R : 0;
-    const float x0 = (float)(cg * VEC);
-    const float Hf = (float)p.H, Rf = (float)p.R;
+    const int x0i = cg * VEC;
     const int row_first = r0 + rr;
-    const float y_first = (float)(row_first % p.H);
-    const float z_first = (float)(row_first / p.H);
+    const int y_first = row_first % p.H;
+    const int z_first = row_first / p.H;
     const uint32_t lds_base = kTma ? smem_u32(smem_raw) + 16u * tid : 0u;
     const unsigned char* gsrc = src + 16ll * tid;
     int it = 0;  // stage counter across both passes (ring position)
 
-    float M = 0.f, invL = 1.f, Ex = 0.f, Ey = 0.f, Ez = 0.f, gx = 0.f, gy = 0.f, gz = 0.f;
+    float M = 0.f, invL = 1.f, gx = 0.f, gy = 0.f, gz = 0.f;
+    double Ex = 0.0, Ey = 0.0, Ez = 0.0;
 
     if constexpr (kHasReduce) {
-        Acc<kSoftmax, VEC> a;
+        Acc<kSoftmax> a;
         a.init();
-        float yf = y_first, zf = z_first;
+        double yd = (double)y_first, zd = (double)z_first;
+        const double Hd = (double)p.H, Rd = (double)p.R;
         for (int i = 0; i < nst; ++i, ++it) {
             float v[kPasses][VEC];
             // ---- fetch the stage into registers ----
@@ -234,108 +261,105 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
 #pragma unroll
                     for (int j = 0; j < VEC; ++j) smax = fmaxf(smax, v[q][j]);
                 if (smax > a.m) {
-                    const float nmL = __fmul_rn(smax, kLog2e);
-                    const float sc = (a.m == kNegInf) ? 0.f : ex2(a.mL - nmL);
-#pragma unroll
-                    for (int j = 0; j < VEC; ++j) a.cx[j] *= sc;
-                    a.sy *= sc;
-                    a.sz *= sc;
+                    a.scale(rebase_weight(a.m, smax));
                     a.m = smax;
-                    a.mL = nmL;
+                    a.mL = __fmul_rn(smax, kLog2e);
                 }
             }
-            // ---- accumulate ----
+            // ---- accumulate: fp32 inside one 16-byte vector, fp64 across vectors ----
             const bool live = kSoftmax ? (a.m != kNegInf) : true;
 #pragma unroll
             for (int q = 0; q < kPasses; ++q) {
                 if (live) {
-                    float rowsum = 0.f;
+                    float rs = 0.f, xs = 0.f;
 #pragma unroll
                     for (int j = 0; j < VEC; ++j) {
                         const float e = kSoftmax ? ex2(fmaf(v[q][j], kLog2e, -a.mL)) : v[q][j];
-                        a.cx[j] += e;
-                        rowsum += e;
+                        rs += e;
+                        if (j) xs = fmaf((float)j, e, xs);
                     }
-                    a.sy = fmaf(yf, rowsum, a.sy);
-                    a.sz = fmaf(zf, rowsum, a.sz);
+                    const double drs = (double)rs;
+                    a.s0 += drs;
+                    a.sx += (double)xs;
+                    a.sy = fma(yd, drs, a.sy);
+                    a.sz = fma(zd, drs, a.sz);
                 }
-                yf += Rf;
-                while (yf >= Hf) {
-                    yf -= Hf;
-                    zf += 1.f;
+                yd += Rd;
+                while (yd >= Hd) {
+                    yd -= Hd;
+                    zd += 1.0;
                 }
             }
         }
 
         // ---- thread -> warp -> CTA ----
-        float l = 0.f, sx = 0.f;
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-            l += a.cx[j];
-            sx = fmaf(x0 + (float)j, a.cx[j], sx);
-        }
-        float sy = a.sy, sz = a.sz, m = a.m;
+        double s0 = a.s0, sy = a.sy, sz = a.sz;
+        double sx = fma((double)x0i, a.s0, a.sx);
+        float m = a.m;
         if constexpr (kSoftmax) {
             const float wm = warp_max(m);
-            const float f = merge_weight(m, wm);
-            l *= f; sx *= f; sy *= f; sz *= f;
+            const double f = (double)rebase_weight(m, wm);
+            s0 *= f; sx *= f; sy *= f; sz *= f;
             m = wm;
         }
-        l = warp_sum(l); sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
+        s0 = warp_sum(s0); sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
         if (lane == 0) {
-            sm.wred[warp][0] = m; sm.wred[warp][1] = l; sm.wred[warp][2] = sx;
-            sm.wred[warp][3] = sy; sm.wred[warp][4] = sz;
+            sm.wred[warp][0] = s0; sm.wred[warp][1] = sx; sm.wred[warp][2] = sy; sm.wred[warp][3] = sz;
+            sm.wmax[warp] = m;
         }
         consumer_barrier();
         if (warp == 0) {
             constexpr int NW = kConsumers / 32;
-            float pm = (lane < NW) ? sm.wred[lane][0] : (kSoftmax ? kNegInf : 0.f);
-            float pl = (lane < NW) ? sm.wred[lane][1] : 0.f;
-            float px = (lane < NW) ? sm.wred[lane][2] : 0.f;
-            float py = (lane < NW) ? sm.wred[lane][3] : 0.f;
-            float pz = (lane < NW) ? sm.wred[lane][4] : 0.f;
+            float pm = (lane < NW) ? sm.wmax[lane] : (kSoftmax ? kNegInf : 0.f);
+            double q0 = (lane < NW) ? sm.wred[lane][0] : 0.0;
+            double q1 = (lane < NW) ? sm.wred[lane][1] : 0.0;
+            double q2 = (lane < NW) ? sm.wred[lane][2] : 0.0;
+            double q3 = (lane < NW) ? sm.wred[lane][3] : 0.0;
             if constexpr (kSoftmax) {
                 const float wm = warp_max(pm);
-                const float f = merge_weight(pm, wm);
-                pl *= f; px *= f; py *= f; pz *= f;
+                const double f = (double)rebase_weight(pm, wm);
+                q0 *= f; q1 *= f; q2 *= f; q3 *= f;
                 pm = wm;
             }
-            pl = warp_sum(pl); px = warp_sum(px); py = warp_sum(py); pz = warp_sum(pz);
+            q0 = warp_sum(q0); q1 = warp_sum(q1); q2 = warp_sum(q2); q3 = warp_sum(q3);
             if (lane == 0) {
-                sm.part[0] = pm; sm.part[1] = pl; sm.part[2] = px; sm.part[3] = py; sm.part[4] = pz;
+                sm.part[0] = q0; sm.part[1] = q1; sm.part[2] = q2; sm.part[3] = q3;
+                sm.part_m = pm;
             }
         }
         // ---- CTA -> cluster (DSMEM) ----
         if (S > 1) {
             cluster_sync_all();  // every CTA's `part` is written and visible cluster-wide
-            if (tid < 5 * (int)S) sm.all[tid / 5][tid % 5] = dsmem_ld_f32(smem_u32(&sm.part[tid % 5]), tid / 5);
+            if (tid < 4 * (int)S) sm.all[tid / 4][tid % 4] = dsmem_ld_f64(smem_u32(&sm.part[tid % 4]), tid / 4);
+            if (tid >= 32 && tid < 32 + (int)S) sm.all_m[tid - 32] = dsmem_ld_f32(smem_u32(&sm.part_m), tid - 32);
             // done reading peers: arrive now, wait before exiting
             consumer_barrier();
             asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
         } else {
             consumer_barrier();
-            if (tid < 5) sm.all[0][tid] = sm.part[tid];
+            if (tid < 4) sm.all[0][tid] = sm.part[tid];
+            if (tid == 4) sm.all_m[0] = sm.part_m;
             consumer_barrier();
         }
         if (tid == 0) {
             float fm = kSoftmax ? kNegInf : 0.f;
             if constexpr (kSoftmax)
-                for (uint32_t r = 0; r < S; ++r) fm = fmaxf(fm, sm.all[r][0]);
-            float fl = 0.f, fx = 0.f, fy = 0.f, fz = 0.f;
+                for (uint32_t r = 0; r < S; ++r) fm = fmaxf(fm, sm.all_m[r]);
+            double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
             for (uint32_t r = 0; r < S; ++r) {
-                const float f = kSoftmax ? merge_weight(sm.all[r][0], fm) : 1.f;
-                fl = fmaf(f, sm.all[r][1], fl);
-                fx = fmaf(f, sm.all[r][2], fx);
-                fy = fmaf(f, sm.all[r][3], fy);
-                fz = fmaf(f, sm.all[r][4], fz);
+                const double f = kSoftmax ? (double)rebase_weight(sm.all_m[r], fm) : 1.0;
+                t0 = fma(f, sm.all[r][0], t0);
+                t1 = fma(f, sm.all[r][1], t1);
+                t2 = fma(f, sm.all[r][2], t2);
+                t3 = fma(f, sm.all[r][3], t3);
             }
-            // loss.py:39-41 (expectations) and :54-56 (normalisation)
-            const float ex_ = kSoftmax ? fx / fl : fx;
-            const float ey_ = kSoftmax ? fy / fl : fy;
-            const float ez_ = kSoftmax ? fz / fl : fz;
-            const float cxn = ex_ / (float)p.W - 0.5f;
-            const float cyn = ey_ / (float)p.H - 0.5f;
-            const float czn = ez_ / (float)p.D - 0.5f;
+            // loss.py:39-41 (expectations) and :54-56 (normalisation), in fp64, rounded once
+            const double ex_ = kSoftmax ? t1 / t0 : t1;
+            const double ey_ = kSoftmax ? t2 / t0 : t2;
+            const double ez_ = kSoftmax ? t3 / t0 : t3;
+            const float cxn = (float)(ex_ / (double)p.W - 0.5);
+            const float cyn = (float)(ey_ / (double)p.H - 0.5);
+            const float czn = (float)(ez_ / (double)p.D - 0.5);
             float g0 = 0.f, g1 = 0.f, g2 = 0.f;
             if constexpr (kOp == OP_FUSED) {
                 // loss.py:86-89 on this volume's three coordinates, in the targets' precision
@@ -364,16 +388,16 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
             if (crank == 0) {
                 if (p.coords) { p.coords[vol * 3 + 0] = cxn; p.coords[vol * 3 + 1] = cyn; p.coords[vol * 3 + 2] = czn; }
                 if (p.expect) { p.expect[vol * 3 + 0] = ex_; p.expect[vol * 3 + 1] = ey_; p.expect[vol * 3 + 2] = ez_; }
-                if (p.stats) { p.stats[vol * 2 + 0] = fm; p.stats[vol * 2 + 1] = fl; }
+                if (p.stats) { p.stats[vol * 2 + 0] = fm; p.stats[vol * 2 + 1] = (float)t0; }
             }
-            sm.fin[0] = fm; sm.fin[1] = fl; sm.fin[2] = ex_; sm.fin[3] = ey_; sm.fin[4] = ez_;
-            sm.fin[5] = g0; sm.fin[6] = g1; sm.fin[7] = g2;
+            sm.finE[0] = ex_; sm.finE[1] = ey_; sm.finE[2] = ez_;
+            sm.fin[0] = fm; sm.fin[1] = (float)t0; sm.fin[2] = g0; sm.fin[3] = g1; sm.fin[4] = g2;
         }
         if constexpr (kOp == OP_FUSED) {
             consumer_barrier();
             M = sm.fin[0]; invL = 1.f / sm.fin[1];
-            Ex = sm.fin[2]; Ey = sm.fin[3]; Ez = sm.fin[4];
-            gx = sm.fin[5]; gy = sm.fin[6]; gz = sm.fin[7];
+            Ex = sm.finE[0]; Ey = sm.finE[1]; Ez = sm.finE[2];
+            gx = sm.fin[2]; gy = sm.fin[3]; gz = sm.fin[4];
         }
     } else {
         // write-only ops read their per-volume scalars from the forward's outputs
@@ -388,9 +412,13 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
 
     if constexpr (kHasWrite) {
         // dlogits_i = e_i/L * ( gx (x-Ex)/W + gy (y-Ey)/H + gz (z-Ez)/D )
+        // (idx - E) must keep its ABSOLUTE accuracy (see the header): x once per thread in fp64,
+        // y and z per row against E split into hi + lo floats.
         const float ML = __fmul_rn(M, kLog2e);
         float ax[VEC];
         float ky = 0.f, kz = 0.f;
+        const float Eyh = (float)Ey, Eyl = (float)(Ey - (double)Eyh);
+        const float Ezh = (float)Ez, Ezl = (float)(Ez - (double)Ezh);
         if constexpr (kOp == OP_WRITE_PROB) {
 #pragma unroll
             for (int j = 0; j < VEC; ++j) ax[j] = invL;
@@ -399,10 +427,11 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
             ky = gy / (float)p.H * invL;
             kz = gz / (float)p.D * invL;
 #pragma unroll
-            for (int j = 0; j < VEC; ++j) ax[j] = kx * (x0 + (float)j - Ex);
+            for (int j = 0; j < VEC; ++j) ax[j] = kx * (float)((double)(x0i + j) - Ex);
         }
         unsigned char* gdst = p.out + vol * p.vol_bytes + (long long)r0 * row_bytes + 16ll * tid;
-        float yf = y_first, zf = z_first;
+        const float Hf = (float)p.H, Rf = (float)p.R;
+        float yf = (float)y_first, zf = (float)z_first;
         for (int i = 0; i < nst; ++i, ++it) {
             float v[kPasses][VEC];
             if constexpr (kTma) {
@@ -424,7 +453,8 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
             for (int q = 0; q < kPasses; ++q) {
                 if (i * kPasses + q < nvis) {
                     float rowterm = 0.f;
-                    if constexpr (kOp != OP_WRITE_PROB) rowterm = fmaf(ky, yf - Ey, kz * (zf - Ez));
+                    if constexpr (kOp != OP_WRITE_PROB)
+                        rowterm = fmaf(ky, (yf - Eyh) - Eyl, kz * ((zf - Ezh) - Ezl));
                     float o[VEC];
 #pragma unroll
                     for (int j = 0; j < VEC; ++j) {
@@ -462,52 +492,55 @@ __global__ void __launch_bounds__(256) k_generic(const Params p) {
     constexpr bool kSoftmax = (kOp != OP_REDUCE_PLAIN);
     constexpr bool kHasReduce = (kOp == OP_REDUCE_SOFTMAX || kOp == OP_REDUCE_PLAIN || kOp == OP_FUSED);
     constexpr bool kHasWrite = (kOp == OP_WRITE_GRAD || kOp == OP_WRITE_PROB || kOp == OP_FUSED);
-    __shared__ float red[8][5];
-    __shared__ float fin[8];
+    __shared__ float redm[8];
+    __shared__ double red[8][4];
+    __shared__ double finE[3];
+    __shared__ float fin[5];
     const long long vol = blockIdx.x;
     const long long V = (long long)p.D * p.H * p.W;
     const unsigned char* src = p.in + vol * p.vol_bytes;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int HW = p.H * p.W;
-    float M = 0.f, L = 1.f, Ex = 0.f, Ey = 0.f, Ez = 0.f, gx = 0.f, gy = 0.f, gz = 0.f;
+    float M = 0.f, L = 1.f, gx = 0.f, gy = 0.f, gz = 0.f;
+    double Ex = 0.0, Ey = 0.0, Ez = 0.0;
 
     if constexpr (kHasReduce) {
         float m = kSoftmax ? kNegInf : 0.f;
         if constexpr (kSoftmax) {
             for (long long i = tid; i < V; i += 256) m = fmaxf(m, ld_elem<T>(src, i));
             m = warp_max(m);
-            if (lane == 0) red[warp][0] = m;
+            if (lane == 0) redm[warp] = m;
             __syncthreads();
-            m = red[0][0];
-            for (int w = 1; w < 8; ++w) m = fmaxf(m, red[w][0]);
+            m = redm[0];
+            for (int w = 1; w < 8; ++w) m = fmaxf(m, redm[w]);
             __syncthreads();
         }
         const float mL = __fmul_rn(m, kLog2e);
-        float l = 0.f, sx = 0.f, sy = 0.f, sz = 0.f;
+        double l = 0.0, sx = 0.0, sy = 0.0, sz = 0.0;
         for (long long i = tid; i < V; i += 256) {
             const float s = ld_elem<T>(src, i);
-            const float e = kSoftmax ? ex2(fmaf(s, kLog2e, -mL)) : s;
+            const double e = (double)(kSoftmax ? ex2(fmaf(s, kLog2e, -mL)) : s);
             const int z = (int)(i / HW);
             const int rem = (int)(i - (long long)z * HW);
             const int y = rem / p.W;
             const int x = rem - y * p.W;
             l += e;
-            sx = fmaf((float)x, e, sx);
-            sy = fmaf((float)y, e, sy);
-            sz = fmaf((float)z, e, sz);
+            sx = fma((double)x, e, sx);
+            sy = fma((double)y, e, sy);
+            sz = fma((double)z, e, sz);
         }
         l = warp_sum(l); sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
-        if (lane == 0) { red[warp][1] = l; red[warp][2] = sx; red[warp][3] = sy; red[warp][4] = sz; }
+        if (lane == 0) { red[warp][0] = l; red[warp][1] = sx; red[warp][2] = sy; red[warp][3] = sz; }
         __syncthreads();
         if (tid == 0) {
-            float fl = 0.f, fx = 0.f, fy = 0.f, fz = 0.f;
-            for (int w = 0; w < 8; ++w) { fl += red[w][1]; fx += red[w][2]; fy += red[w][3]; fz += red[w][4]; }
-            const float ex_ = kSoftmax ? fx / fl : fx;
-            const float ey_ = kSoftmax ? fy / fl : fy;
-            const float ez_ = kSoftmax ? fz / fl : fz;
-            const float cxn = ex_ / (float)p.W - 0.5f;
-            const float cyn = ey_ / (float)p.H - 0.5f;
-            const float czn = ez_ / (float)p.D - 0.5f;
+            double fl = 0.0, fx = 0.0, fy = 0.0, fz = 0.0;
+            for (int w = 0; w < 8; ++w) { fl += red[w][0]; fx += red[w][1]; fy += red[w][2]; fz += red[w][3]; }
+            const double ex_ = kSoftmax ? fx / fl : fx;
+            const double ey_ = kSoftmax ? fy / fl : fy;
+            const double ez_ = kSoftmax ? fz / fl : fz;
+            const float cxn = (float)(ex_ / (double)p.W - 0.5);
+            const float cyn = (float)(ey_ / (double)p.H - 0.5);
+            const float czn = (float)(ez_ / (double)p.D - 0.5);
             float g[3] = {0.f, 0.f, 0.f};
             if constexpr (kOp == OP_FUSED) {
                 const double c[3] = {(double)cxn, (double)cyn, (double)czn};
@@ -524,13 +557,13 @@ __global__ void __launch_bounds__(256) k_generic(const Params p) {
             }
             if (p.coords) { p.coords[vol * 3 + 0] = cxn; p.coords[vol * 3 + 1] = cyn; p.coords[vol * 3 + 2] = czn; }
             if (p.expect) { p.expect[vol * 3 + 0] = ex_; p.expect[vol * 3 + 1] = ey_; p.expect[vol * 3 + 2] = ez_; }
-            if (p.stats) { p.stats[vol * 2 + 0] = m; p.stats[vol * 2 + 1] = fl; }
-            fin[0] = m; fin[1] = fl; fin[2] = ex_; fin[3] = ey_; fin[4] = ez_;
-            fin[5] = g[0]; fin[6] = g[1]; fin[7] = g[2];
+            if (p.stats) { p.stats[vol * 2 + 0] = m; p.stats[vol * 2 + 1] = (float)fl; }
+            finE[0] = ex_; finE[1] = ey_; finE[2] = ez_;
+            fin[0] = m; fin[1] = (float)fl; fin[2] = g[0]; fin[3] = g[1]; fin[4] = g[2];
         }
         __syncthreads();
-        M = fin[0]; L = fin[1]; Ex = fin[2]; Ey = fin[3]; Ez = fin[4];
-        gx = fin[5]; gy = fin[6]; gz = fin[7];
+        M = fin[0]; L = fin[1]; Ex = finE[0]; Ey = finE[1]; Ez = finE[2];
+        gx = fin[2]; gy = fin[3]; gz = fin[4];
     } else {
         M = p.stats_in[vol * 2 + 0];
         L = p.stats_in[vol * 2 + 1];
@@ -556,7 +589,8 @@ __global__ void __launch_bounds__(256) k_generic(const Params p) {
                 const int rem = (int)(i - (long long)z * HW);
                 const int y = rem / p.W;
                 const int x = rem - y * p.W;
-                o = e * (kx * ((float)x - Ex) + fmaf(ky, (float)y - Ey, kz * ((float)z - Ez)));
+                const float dx = (float)((double)x - Ex), dy = (float)((double)y - Ey), dz = (float)((double)z - Ez);
+                o = e * (kx * dx + fmaf(ky, dy, kz * dz));
             }
             dst[i] = Vec16<T>::from_f32(o);
         }
@@ -644,7 +678,7 @@ static int dispatch(Params p, int cluster, int variant, cudaStream_t st) {
 }
 
 static int check_geom(const void* in, int dtype, long long n_vol, int D, int H, int W, int cluster, int variant) {
-    if (!in) return HIPE_E_NULL;
+    if (!in && n_vol != 0) return HIPE_E_NULL;
     if (dtype != HIPE_F32 && dtype != HIPE_BF16) return HIPE_E_DTYPE;
     if (n_vol < 0 || D <= 0 || H <= 0 || W <= 0) return HIPE_E_SHAPE;
     if ((long long)D * H * W > (1ll << 31)) return HIPE_E_SHAPE;
@@ -668,10 +702,11 @@ static int dispatch_dtype(const Params& p, int dtype, int cluster, int variant, 
 using namespace hipe;
 
 extern "C" int hipe_softargmax_fwd(const void* logits, int dtype, long long n_vol, int D, int H, int W,
-                                   int apply_softmax, float* coords, float* expect, float* stats,
+                                   int apply_softmax, float* coords, double* expect, float* stats,
                                    int cluster, int variant, void* stream) {
     int rc = check_geom(logits, dtype, n_vol, D, H, W, cluster, variant);
     if (rc) return rc;
+    if (n_vol == 0) return 0;
     Params p = {};
     p.in = static_cast<const unsigned char*>(logits);
     p.n_vol = n_vol; p.D = D; p.H = H; p.W = W;
@@ -682,11 +717,12 @@ extern "C" int hipe_softargmax_fwd(const void* logits, int dtype, long long n_vo
 }
 
 extern "C" int hipe_softargmax_bwd(const void* logits, int dtype, long long n_vol, int D, int H, int W,
-                                   const float* stats, const float* expect, const float* gcoords,
+                                   const float* stats, const double* expect, const float* gcoords,
                                    const float* gscale, void* dlogits, int cluster, int variant,
                                    void* stream) {
     int rc = check_geom(logits, dtype, n_vol, D, H, W, cluster, variant);
     if (rc) return rc;
+    if (n_vol == 0) return 0;
     if (!stats || !expect || !gcoords || !dlogits) return HIPE_E_NULL;
     Params p = {};
     p.in = static_cast<const unsigned char*>(logits);
@@ -702,6 +738,7 @@ extern "C" int hipe_volume_softmax(const void* logits, int dtype, long long n_vo
                                    void* stream) {
     int rc = check_geom(logits, dtype, n_vol, D, H, W, cluster, variant);
     if (rc) return rc;
+    if (n_vol == 0) return 0;
     if (!stats || !probs) return HIPE_E_NULL;
     Params p = {};
     p.in = static_cast<const unsigned char*>(logits);
@@ -714,10 +751,11 @@ extern "C" int hipe_volume_softmax(const void* logits, int dtype, long long n_vo
 
 extern "C" int hipe_joint_loss_fused(const void* logits, int dtype, long long n_vol, int D, int H, int W,
                                      const void* gt, const void* vis, int tgt_dtype, double norm,
-                                     float* coords, float* expect, float* stats, double* loss_terms,
+                                     float* coords, double* expect, float* stats, double* loss_terms,
                                      void* dlogits, int cluster, int variant, void* stream) {
     int rc = check_geom(logits, dtype, n_vol, D, H, W, cluster, variant);
     if (rc) return rc;
+    if (n_vol == 0) return 0;
     if (!gt || !vis || !dlogits) return HIPE_E_NULL;
     if (tgt_dtype != HIPE_F32 && tgt_dtype != HIPE_F64) return HIPE_E_DTYPE;
     Params p = {};

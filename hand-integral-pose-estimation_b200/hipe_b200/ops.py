@@ -68,7 +68,8 @@ def _ptr(t):
 
 
 def softargmax_forward(logits, n_vol, D, H, W, apply_softmax=True, cluster=None, variant=None):
-    """-> coords (n_vol,3) [x/W-.5, y/H-.5, z/D-.5], expect (n_vol,3) voxel units, stats (n_vol,2)."""
+    """-> coords (n_vol,3) fp32 [x/W-.5, y/H-.5, z/D-.5], expect (n_vol,3) fp64 voxel units,
+    stats (n_vol,2) fp32 (max, sum exp)."""
     _need_cuda(logits, "heatmaps")
     code = _logits_code(logits)
     if not logits.is_contiguous():
@@ -77,7 +78,7 @@ def softargmax_forward(logits, n_vol, D, H, W, apply_softmax=True, cluster=None,
         raise ValueError("heatmaps have %d elements, expected %d x %dx%dx%d" % (logits.numel(), n_vol, D, H, W))
     dev = logits.device
     coords = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
-    expect = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
+    expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev)
     stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev), _launch("softargmax_fwd", logits):
         check(_lib.load().hipe_softargmax_fwd(
@@ -96,6 +97,7 @@ def softargmax_backward(logits, n_vol, D, H, W, stats, expect, gcoords, gscale=N
     if not logits.is_contiguous():
         logits = logits.contiguous()
     gcoords = gcoords.to(device=logits.device, dtype=torch.float32).contiguous()
+    expect = expect.to(device=logits.device, dtype=torch.float64).contiguous()
     if gscale is not None:
         gscale = gscale.to(device=logits.device, dtype=torch.float32).reshape(1).contiguous()
     out = torch.empty_like(logits)
@@ -171,7 +173,7 @@ def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, varian
     gt, vis, tcode, _ = _targets(coords, gt, vis)
     if gt.numel() != n_vol * 3 or vis.numel() != n_vol * 3:
         raise ValueError("targets must hold 3 values per volume")
-    expect = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
+    expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev)
     stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
     terms = torch.empty((n_vol * 3,), dtype=torch.float64, device=dev)
     dlogits = torch.empty_like(logits)

@@ -31,7 +31,7 @@ def generate_3d_integral_preds_tensor(heatmaps, num_joints, x_dim, y_dim, z_dim)
     assert isinstance(heatmaps, torch.Tensor)
     B = heatmaps.shape[0]
     _, expect, _ = ops.softargmax_forward(heatmaps, B * num_joints, z_dim, y_dim, x_dim, apply_softmax=False)
-    e = expect.view(B, num_joints, 3).to(heatmaps.dtype if heatmaps.dtype == torch.float32 else torch.float32)
+    e = expect.view(B, num_joints, 3).to(torch.float32)
     return e[:, :, 0:1], e[:, :, 1:2], e[:, :, 2:3]
 
 

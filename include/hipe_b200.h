@@ -60,14 +60,16 @@ HIPE_API const char* hipe_strerror(int code);
  * on already-normalised heatmaps.
  *   logits_dev : n_vol * D*H*W elements of `dtype` (HIPE_F32 | HIPE_BF16), read-only
  *   coords_dev : n_vol*3 floats  (x/W-0.5, y/H-0.5, z/D-0.5)  -- loss.py:54-58   (nullable)
- *   expect_dev : n_vol*3 floats  raw expectations in voxel units -- loss.py:39-41 (nullable)
+ *   expect_dev : n_vol*3 DOUBLES raw expectations in voxel units -- loss.py:39-41 (nullable);
+ *                fp64 because the backward needs (idx - E) to ~1e-7 voxel, below fp32's
+ *                resolution at E ~ 32
  *   stats_dev  : n_vol*2 floats  (max logit, sum exp(logit-max)); input of the backward
  *                (nullable; written as (0, sum) when apply_softmax == 0)
  *   cluster    : CTAs cooperating on one volume: 0 = auto, else 1|2|4|8
  *   variant    : HIPE_VARIANT_*
  */
 HIPE_API int hipe_softargmax_fwd(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
-                        int apply_softmax, float* coords_dev, float* expect_dev,
+                        int apply_softmax, float* coords_dev, double* expect_dev,
                         float* stats_dev, int cluster, int variant, void* stream);
 
 /*
@@ -79,7 +81,7 @@ HIPE_API int hipe_softargmax_fwd(const void* logits_dev, int dtype, long long n_
  *   dlogits_dev : n_vol * D*H*W elements of `dtype`
  */
 HIPE_API int hipe_softargmax_bwd(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
-                        const float* stats_dev, const float* expect_dev,
+                        const float* stats_dev, const double* expect_dev,
                         const float* gcoords_dev, const float* gscale_dev, void* dlogits_dev,
                         int cluster, int variant, void* stream);
 
@@ -112,7 +114,7 @@ HIPE_API int hipe_l1_loss_fwd(const float* coords_dev, const void* gt_dev, const
  */
 HIPE_API int hipe_joint_loss_fused(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
                           const void* gt_dev, const void* vis_dev, int tgt_dtype, double norm,
-                          float* coords_dev, float* expect_dev, float* stats_dev,
+                          float* coords_dev, double* expect_dev, float* stats_dev,
                           double* loss_terms_dev /* n_vol*3 */, void* dlogits_dev,
                           int cluster, int variant, void* stream);
 
