@@ -59,6 +59,7 @@ struct Params {
     int G;   // 16-byte column groups per row
     int R;   // rows per visit of the CTA
     int NR;  // rows per volume
+    int nv2;      // reduce pass reads two adjacent 16-byte vectors per visit (rows are 32-byte multiples)
     int reverse;
     int pol1, pol2;  // L2 policy of the TMA loads of pass 1 / pass 2: 0 normal, 1 evict_first, 2 evict_last
     // reduce outputs
@@ -96,386 +97,11 @@ __device__ __forceinline__ void consumer_barrier() {
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
 }
 
-template <bool kSoftmax>
-struct Acc {
-    float m;    // running max (natural units)
-    float mL;   // fl(m * log2e): the exponent offset every e of this thread is relative to
-    double s0;  // sum e
-    double sx;  // sum e * (x - x0)   (x0 = the thread's first column)
-    double sy;  // sum e * y
-    double sz;  // sum e * z
-    __device__ __forceinline__ void init() {
-        m = kSoftmax ? kNegInf : 0.f;
-        mL = kSoftmax ? kNegInf : 0.f;
-        s0 = sx = sy = sz = 0.0;
-    }
-    __device__ __forceinline__ void scale(float f) {
-        const double d = (double)f;
-        s0 *= d; sx *= d; sy *= d; sz *= d;
-    }
-};
+}  // namespace hipe
 
-// Weight that re-bases a partial computed against maximum m_from onto maximum m_to >= m_from.
-// Every exponential is 2^(s*log2e - fl(m*log2e)), so the weight is 2^(fl(m_from*log2e) -
-// fl(m_to*log2e)) with the SAME rounded products (no contraction): a partial is re-based by
-// exactly the offset its exponentials were computed against.
-__device__ __forceinline__ float rebase_weight(float m_from, float m_to) {
-    return (m_from == kNegInf) ? 0.f
-                               : ex2(__fsub_rn(__fmul_rn(m_from, kLog2e), __fmul_rn(m_to, kLog2e)));
-}
+#include "hipe_stream_kernel.cuh"
 
-template <typename T, bool kTma, int kOp>
-__global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
-    k_stream(const Params p) {
-    using V16 = Vec16<T>;
-    constexpr int VEC = V16::N;
-    constexpr bool kHasReduce = (kOp == OP_REDUCE_SOFTMAX || kOp == OP_REDUCE_PLAIN || kOp == OP_FUSED);
-    constexpr bool kHasWrite = (kOp == OP_WRITE_GRAD || kOp == OP_WRITE_PROB || kOp == OP_FUSED);
-    constexpr bool kSoftmax = (kOp != OP_REDUCE_PLAIN);
-    constexpr int kNumPassesOverVolume = (kOp == OP_FUSED) ? 2 : 1;
-
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    SmemLayout& sm = *reinterpret_cast<SmemLayout*>(smem_raw + (kTma ? kStages * kStageBytes : 0));
-
-    const int tid = threadIdx.x;
-    const uint32_t S = cluster_nctarank();
-    const uint32_t crank = cluster_ctarank();
-    long long vol = blockIdx.x / S;
-    if (p.reverse) vol = p.n_vol - 1 - vol;
-
-    // this CTA's rows
-    const int r0 = (int)(((long long)p.NR * crank) / S);
-    const int r1 = (int)(((long long)p.NR * (crank + 1)) / S);
-    const int nrows = r1 - r0;
-    const int row_bytes = p.G * 16;
-    const int pass_bytes = p.R * row_bytes;
-    const long long cta_bytes = (long long)nrows * row_bytes;
-    const int stage_bytes = kPasses * pass_bytes;
-    const int nst = (int)((cta_bytes + stage_bytes - 1) / stage_bytes);
-    const unsigned char* src = p.in + vol * p.vol_bytes + (long long)r0 * row_bytes;
-
-    // ---------------- barrier setup (TMA variant) ----------------
-    if constexpr (kTma) {
-        if (tid == 0) {
-#pragma unroll
-            for (int s = 0; s < kStages; ++s) {
-                mbar_init(smem_u32(&sm.full[s]), 1);
-                mbar_init(smem_u32(&sm.empty[s]), kConsumers / 32);
-            }
-            mbar_fence_init();
-            fence_proxy_async();
-        }
-        __syncthreads();
-
-        if (tid >= kConsumers) {
-            // ---------------- producer warp ----------------
-            // It has nothing to contribute to the cluster reduction: arrive right away so the
-            // consumers' cluster barrier can complete while this warp is still streaming.
-            if (S > 1 && kHasReduce) asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-            if (tid == kConsumers) {
-                const uint64_t pn = policy_evict_normal(), pf = policy_evict_first(), pl = policy_evict_last();
-                const uint64_t pol_a = p.pol1 == 0 ? pn : (p.pol1 == 1 ? pf : pl);
-                const uint64_t pol_b = p.pol2 == 0 ? pn : (p.pol2 == 1 ? pf : pl);
-                const int total = nst * kNumPassesOverVolume;
-                for (int it = 0; it < total; ++it) {
-                    const int slot = it % kStages;
-                    const int i = (it >= nst) ? it - nst : it;
-                    if (it >= kStages) mbar_wait(smem_u32(&sm.empty[slot]), ((it / kStages) - 1) & 1);
-                    const long long off = (long long)i * stage_bytes;
-                    const long long left = cta_bytes - off;
-                    const uint32_t bytes = (uint32_t)(left < stage_bytes ? left : stage_bytes);
-                    const uint32_t bar = smem_u32(&sm.full[slot]);
-                    mbar_arrive_expect_tx(bar, bytes);
-                    tma_load_1d(smem_u32(smem_raw + slot * kStageBytes), src + off, bytes, bar,
-                                (it < nst) ? pol_a : pol_b);
-                }
-            }
-            __syncwarp();
-            if (S > 1 && kHasReduce) {
-                asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-                // second cluster phase: peers must not exit while their `part` is being read
-                asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-                asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-            }
-            return;
-        }
-    }
-
-    // ---------------- consumers ----------------
-    const int lane = tid & 31;
-    const int warp = tid >> 5;
-    const bool active = tid < p.G * p.R;
-    const int cg = active ? tid % p.G : 0;
-    const int rr = active ? tid / p.G : 0;
-    // number of row visits of this thread inside the CTA's range
-    const int nvis = (active && nrows > rr) ? (nrows - rr + p.R - 1) / p.R : 0;
-    const int x0i = cg * VEC;
-    const int row_first = r0 + rr;
-    const int y_first = row_first % p.H;
-    const int z_first = row_first / p.H;
-    const uint32_t lds_base = kTma ? smem_u32(smem_raw) + 16u * tid : 0u;
-    const unsigned char* gsrc = src + 16ll * tid;
-    int it = 0;  // stage counter across both passes (ring position)
-
-    float M = 0.f, invL = 1.f, gx = 0.f, gy = 0.f, gz = 0.f;
-    double Ex = 0.0, Ey = 0.0, Ez = 0.0;
-
-    if constexpr (kHasReduce) {
-        Acc<kSoftmax> a;
-        a.init();
-        double yd = (double)y_first, zd = (double)z_first;
-        const double Hd = (double)p.H, Rd = (double)p.R;
-        for (int i = 0; i < nst; ++i, ++it) {
-            float v[kPasses][VEC];
-            // ---- fetch the stage into registers ----
-            if constexpr (kTma) {
-                const int slot = it % kStages;
-                mbar_wait(smem_u32(&sm.full[slot]), (it / kStages) & 1);
-#pragma unroll
-                for (int q = 0; q < kPasses; ++q) {
-                    if (i * kPasses + q < nvis) {
-                        V16::unpack(lds128(lds_base + slot * kStageBytes + q * pass_bytes), v[q]);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < VEC; ++j) v[q][j] = kSoftmax ? kNegInf : 0.f;
-                    }
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(&sm.empty[slot]));
-            } else {
-#pragma unroll
-                for (int q = 0; q < kPasses; ++q) {
-                    if (i * kPasses + q < nvis) {
-                        V16::unpack(ldg_stream(gsrc + (long long)(i * kPasses + q) * pass_bytes), v[q]);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < VEC; ++j) v[q][j] = kSoftmax ? kNegInf : 0.f;
-                    }
-                }
-            }
-            // ---- online max ----
-            if constexpr (kSoftmax) {
-                float smax = kNegInf;
-#pragma unroll
-                for (int q = 0; q < kPasses; ++q)
-#pragma unroll
-                    for (int j = 0; j < VEC; ++j) smax = fmaxf(smax, v[q][j]);
-                if (smax > a.m) {
-                    a.scale(rebase_weight(a.m, smax));
-                    a.m = smax;
-                    a.mL = __fmul_rn(smax, kLog2e);
-                }
-            }
-            // ---- accumulate: fp32 inside one 16-byte vector, fp64 across vectors ----
-            const bool live = kSoftmax ? (a.m != kNegInf) : true;
-#pragma unroll
-            for (int q = 0; q < kPasses; ++q) {
-                if (live) {
-                    float rs = 0.f, xs = 0.f;
-#pragma unroll
-                    for (int j = 0; j < VEC; ++j) {
-                        const float e = kSoftmax ? ex2(fmaf(v[q][j], kLog2e, -a.mL)) : v[q][j];
-                        rs += e;
-                        if (j) xs = fmaf((float)j, e, xs);
-                    }
-                    const double drs = (double)rs;
-                    a.s0 += drs;
-                    a.sx += (double)xs;
-                    a.sy = fma(yd, drs, a.sy);
-                    a.sz = fma(zd, drs, a.sz);
-                }
-                yd += Rd;
-                while (yd >= Hd) {
-                    yd -= Hd;
-                    zd += 1.0;
-                }
-            }
-        }
-
-        // ---- thread -> warp -> CTA ----
-        double s0 = a.s0, sy = a.sy, sz = a.sz;
-        double sx = fma((double)x0i, a.s0, a.sx);
-        float m = a.m;
-        if constexpr (kSoftmax) {
-            const float wm = warp_max(m);
-            const double f = (double)rebase_weight(m, wm);
-            s0 *= f; sx *= f; sy *= f; sz *= f;
-            m = wm;
-        }
-        s0 = warp_sum(s0); sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
-        if (lane == 0) {
-            sm.wred[warp][0] = s0; sm.wred[warp][1] = sx; sm.wred[warp][2] = sy; sm.wred[warp][3] = sz;
-            sm.wmax[warp] = m;
-        }
-        consumer_barrier();
-        if (warp == 0) {
-            constexpr int NW = kConsumers / 32;
-            float pm = (lane < NW) ? sm.wmax[lane] : (kSoftmax ? kNegInf : 0.f);
-            double q0 = (lane < NW) ? sm.wred[lane][0] : 0.0;
-            double q1 = (lane < NW) ? sm.wred[lane][1] : 0.0;
-            double q2 = (lane < NW) ? sm.wred[lane][2] : 0.0;
-            double q3 = (lane < NW) ? sm.wred[lane][3] : 0.0;
-            if constexpr (kSoftmax) {
-                const float wm = warp_max(pm);
-                const double f = (double)rebase_weight(pm, wm);
-                q0 *= f; q1 *= f; q2 *= f; q3 *= f;
-                pm = wm;
-            }
-            q0 = warp_sum(q0); q1 = warp_sum(q1); q2 = warp_sum(q2); q3 = warp_sum(q3);
-            if (lane == 0) {
-                sm.part[0] = q0; sm.part[1] = q1; sm.part[2] = q2; sm.part[3] = q3;
-                sm.part_m = pm;
-            }
-        }
-        // ---- CTA -> cluster (DSMEM) ----
-        if (S > 1) {
-            cluster_sync_all();  // every CTA's `part` is written and visible cluster-wide
-            if (tid < 4 * (int)S) sm.all[tid / 4][tid % 4] = dsmem_ld_f64(smem_u32(&sm.part[tid % 4]), tid / 4);
-            if (tid >= 32 && tid < 32 + (int)S) sm.all_m[tid - 32] = dsmem_ld_f32(smem_u32(&sm.part_m), tid - 32);
-            // done reading peers: arrive now, wait before exiting
-            consumer_barrier();
-            asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-        } else {
-            consumer_barrier();
-            if (tid < 4) sm.all[0][tid] = sm.part[tid];
-            if (tid == 4) sm.all_m[0] = sm.part_m;
-            consumer_barrier();
-        }
-        if (tid == 0) {
-            float fm = kSoftmax ? kNegInf : 0.f;
-            if constexpr (kSoftmax)
-                for (uint32_t r = 0; r < S; ++r) fm = fmaxf(fm, sm.all_m[r]);
-            double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
-            for (uint32_t r = 0; r < S; ++r) {
-                const double f = kSoftmax ? (double)rebase_weight(sm.all_m[r], fm) : 1.0;
-                t0 = fma(f, sm.all[r][0], t0);
-                t1 = fma(f, sm.all[r][1], t1);
-                t2 = fma(f, sm.all[r][2], t2);
-                t3 = fma(f, sm.all[r][3], t3);
-            }
-            // loss.py:39-41 (expectations) and :54-56 (normalisation), in fp64, rounded once
-            const double ex_ = kSoftmax ? t1 / t0 : t1;
-            const double ey_ = kSoftmax ? t2 / t0 : t2;
-            const double ez_ = kSoftmax ? t3 / t0 : t3;
-            const float cxn = (float)(ex_ / (double)p.W - 0.5);
-            const float cyn = (float)(ey_ / (double)p.H - 0.5);
-            const float czn = (float)(ez_ / (double)p.D - 0.5);
-            float g0 = 0.f, g1 = 0.f, g2 = 0.f;
-            if constexpr (kOp == OP_FUSED) {
-                // loss.py:86-89 on this volume's three coordinates, in the targets' precision
-                double t[3], w[3];
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    if (p.tgt_f64) {
-                        t[k] = reinterpret_cast<const double*>(p.gt)[vol * 3 + k];
-                        w[k] = reinterpret_cast<const double*>(p.vis)[vol * 3 + k];
-                    } else {
-                        t[k] = reinterpret_cast<const float*>(p.gt)[vol * 3 + k];
-                        w[k] = reinterpret_cast<const float*>(p.vis)[vol * 3 + k];
-                    }
-                }
-                const double c[3] = {(double)cxn, (double)cyn, (double)czn};
-                float g[3];
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const double dlt = c[k] - t[k];
-                    const double sg = (dlt > 0.0) ? 1.0 : ((dlt < 0.0) ? -1.0 : 0.0);
-                    g[k] = (float)(sg * w[k] * p.norm);
-                    if (crank == 0 && p.loss_terms) p.loss_terms[vol * 3 + k] = fabs(dlt) * w[k];
-                }
-                g0 = g[0]; g1 = g[1]; g2 = g[2];
-            }
-            if (crank == 0) {
-                if (p.coords) { p.coords[vol * 3 + 0] = cxn; p.coords[vol * 3 + 1] = cyn; p.coords[vol * 3 + 2] = czn; }
-                if (p.expect) { p.expect[vol * 3 + 0] = ex_; p.expect[vol * 3 + 1] = ey_; p.expect[vol * 3 + 2] = ez_; }
-                if (p.stats) { p.stats[vol * 2 + 0] = fm; p.stats[vol * 2 + 1] = (float)t0; }
-            }
-            sm.finE[0] = ex_; sm.finE[1] = ey_; sm.finE[2] = ez_;
-            sm.fin[0] = fm; sm.fin[1] = (float)t0; sm.fin[2] = g0; sm.fin[3] = g1; sm.fin[4] = g2;
-        }
-        if constexpr (kOp == OP_FUSED) {
-            consumer_barrier();
-            M = sm.fin[0]; invL = 1.f / sm.fin[1];
-            Ex = sm.finE[0]; Ey = sm.finE[1]; Ez = sm.finE[2];
-            gx = sm.fin[2]; gy = sm.fin[3]; gz = sm.fin[4];
-        }
-    } else {
-        // write-only ops read their per-volume scalars from the forward's outputs
-        M = p.stats_in[vol * 2 + 0];
-        invL = 1.f / p.stats_in[vol * 2 + 1];
-        if constexpr (kOp == OP_WRITE_GRAD) {
-            const float gs = p.gscale ? *p.gscale : 1.f;
-            Ex = p.expect_in[vol * 3 + 0]; Ey = p.expect_in[vol * 3 + 1]; Ez = p.expect_in[vol * 3 + 2];
-            gx = p.gcoords[vol * 3 + 0] * gs; gy = p.gcoords[vol * 3 + 1] * gs; gz = p.gcoords[vol * 3 + 2] * gs;
-        }
-    }
-
-    if constexpr (kHasWrite) {
-        // dlogits_i = e_i/L * ( gx (x-Ex)/W + gy (y-Ey)/H + gz (z-Ez)/D )
-        // (idx - E) must keep its ABSOLUTE accuracy (see the header): x once per thread in fp64,
-        // y and z per row against E split into hi + lo floats.
-        const float ML = __fmul_rn(M, kLog2e);
-        float ax[VEC];
-        float ky = 0.f, kz = 0.f;
-        const float Eyh = (float)Ey, Eyl = (float)(Ey - (double)Eyh);
-        const float Ezh = (float)Ez, Ezl = (float)(Ez - (double)Ezh);
-        if constexpr (kOp == OP_WRITE_PROB) {
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) ax[j] = invL;
-        } else {
-            const float kx = gx / (float)p.W * invL;
-            ky = gy / (float)p.H * invL;
-            kz = gz / (float)p.D * invL;
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) ax[j] = kx * (float)((double)(x0i + j) - Ex);
-        }
-        unsigned char* gdst = p.out + vol * p.vol_bytes + (long long)r0 * row_bytes + 16ll * tid;
-        const float Hf = (float)p.H, Rf = (float)p.R;
-        float yf = (float)y_first, zf = (float)z_first;
-        for (int i = 0; i < nst; ++i, ++it) {
-            float v[kPasses][VEC];
-            if constexpr (kTma) {
-                const int slot = it % kStages;
-                mbar_wait(smem_u32(&sm.full[slot]), (it / kStages) & 1);
-#pragma unroll
-                for (int q = 0; q < kPasses; ++q)
-                    if (i * kPasses + q < nvis)
-                        V16::unpack(lds128(lds_base + slot * kStageBytes + q * pass_bytes), v[q]);
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(&sm.empty[slot]));
-            } else {
-#pragma unroll
-                for (int q = 0; q < kPasses; ++q)
-                    if (i * kPasses + q < nvis)
-                        V16::unpack(ldg_stream(gsrc + (long long)(i * kPasses + q) * pass_bytes), v[q]);
-            }
-#pragma unroll
-            for (int q = 0; q < kPasses; ++q) {
-                if (i * kPasses + q < nvis) {
-                    float rowterm = 0.f;
-                    if constexpr (kOp != OP_WRITE_PROB)
-                        rowterm = fmaf(ky, (yf - Eyh) - Eyl, kz * ((zf - Ezh) - Ezl));
-                    float o[VEC];
-#pragma unroll
-                    for (int j = 0; j < VEC; ++j) {
-                        const float e = ex2(fmaf(v[q][j], kLog2e, -ML));
-                        o[j] = e * (ax[j] + rowterm);
-                    }
-                    stg_stream(gdst + (long long)(i * kPasses + q) * pass_bytes, V16::pack(o));
-                }
-                yf += Rf;
-                while (yf >= Hf) {
-                    yf -= Hf;
-                    zf += 1.f;
-                }
-            }
-        }
-    }
-
-    if constexpr (kHasReduce) {
-        if (S > 1) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-    }
-}
+namespace hipe {
 
 // ---------------------------------------------------------------------------------------
 // Generic scalar kernels for shapes the vector path cannot take (row bytes not a multiple
@@ -610,11 +236,17 @@ static int check_device() {
     return major == 10 ? 0 : HIPE_E_ARCH;
 }
 
-static int pick_cluster(long long n_vol, long long vol_bytes, int NR) {
-    // Aim for >= ~6 resident-CTA waves worth of work items over 148 SMs while keeping every
-    // CTA's share >= 64 KB so the per-CTA prologue/reduction stays a small fraction.
+static int pick_cluster(int op, long long n_vol, long long vol_bytes, int NR) {
+    // Write-only and fused launches: aim for >= ~8 waves of 3 resident CTAs over 148 SMs while
+    // keeping every CTA's share >= 64 KB (finer grain = shorter tail; no reduction to pay for).
+    // Reduce-only launches pay a cluster barrier + DSMEM merge per CTA, so they split a volume
+    // only when there are too few volumes to fill the machine twice over (measured on B200:
+    // 1344 x 1 MiB volumes run 0.236 ms at S=1, 0.291 ms at S=4).
+    const bool reduce_only = (op == OP_REDUCE_SOFTMAX || op == OP_REDUCE_PLAIN);
+    const long long want = reduce_only ? 148ll * 6 : 148ll * 24;
+    const long long min_share = reduce_only ? 131072 : 65536;
     int S = 1;
-    while (S < kMaxCluster && n_vol * S < 148ll * 24 && vol_bytes / (2 * S) >= 65536 && NR / (2 * S) >= 1) S *= 2;
+    while (S < kMaxCluster && n_vol * S < want && vol_bytes / (2 * S) >= min_share && NR / (2 * S) >= 1) S *= 2;
     return S;
 }
 
@@ -671,9 +303,13 @@ static int dispatch(Params p, int cluster, int variant, cudaStream_t st) {
     }
     p.G = (int)(row_b / 16);
     p.R = kConsumers / p.G;
-    int S = cluster ? cluster : pick_cluster(p.n_vol, p.vol_bytes, p.NR);
+    int S = cluster ? cluster : pick_cluster(kOp, p.n_vol, p.vol_bytes, p.NR);
     while (S > 1 && p.NR < S) S /= 2;
     const bool tma = (variant == HIPE_VARIANT_AUTO) ? true : (variant == HIPE_VARIANT_TMA);
+    // two adjacent vectors per visit in the reduce pass when rows are 32-byte multiples (shared
+    // memory reads only: from global memory it would fetch every 32-byte sector twice)
+    p.nv2 = (tma && p.G % 2 == 0) ? 1 : 0;
+    if (const char* e = getenv("HIPE_NV2")) p.nv2 = (p.nv2 && e[0] != '0') ? 1 : 0;
     return tma ? launch_stream<T, true, kOp>(p, S, st) : launch_stream<T, false, kOp>(p, S, st);
 }
 
