@@ -38,6 +38,12 @@ __device__ __forceinline__ void stg_stream(void* p, const uint4& v) {
                  : "memory");
 }
 
+__device__ __forceinline__ void stg_stream_hint(void* p, const uint4& v, uint64_t policy) {
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p),
+                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(policy)
+                 : "memory");
+}
+
 __device__ __forceinline__ uint4 lds128(uint32_t saddr) {
     uint4 r;
     asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"

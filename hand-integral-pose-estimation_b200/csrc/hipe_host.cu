@@ -28,7 +28,7 @@ extern "C" const char* hipe_strerror(int code) {
         case HIPE_E_SHAPE: return "bad shape or size argument";
         case HIPE_E_ALIGN: return "pointer not aligned to its element size";
         case HIPE_E_NULL: return "required pointer is NULL";
-        case HIPE_E_CLUSTER: return "cluster size must be 0, 1, 2, 4 or 8";
+        case HIPE_E_CLUSTER: return "cluster size must be 0, 1, 2, 4, 8 or 16";
         case HIPE_E_ARCH: return "current device is not sm_100 (Blackwell B200)";
         default: break;
     }

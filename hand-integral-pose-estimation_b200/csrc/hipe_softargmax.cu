@@ -40,7 +40,7 @@ constexpr int kConsumers = 256;                   // consumer threads per CTA
 constexpr int kPasses = 4;                        // 16-byte vectors per thread per stage
 constexpr int kStages = 4;                        // TMA ring depth
 constexpr int kStageBytes = kPasses * kConsumers * 16;  // 16 KB
-constexpr int kMaxCluster = 8;
+constexpr int kMaxCluster = 16;                  // 16 is non-portable (opt-in attribute), used by the resident fused launch
 
 enum Op : int {
     OP_REDUCE_SOFTMAX = 0,  // forward
@@ -61,6 +61,8 @@ struct Params {
     int NR;  // rows per volume
     int nv2;      // reduce pass reads two adjacent 16-byte vectors per visit (rows are 32-byte multiples)
     int reverse;
+    int st_hint;     // gradient stores carry an L2 evict_first hint
+    int resident;    // fused launch: every CTA's share fits the ring, pass 2 re-reads shared memory not L2/HBM
     int pol1, pol2;  // L2 policy of the TMA loads of pass 1 / pass 2: 0 normal, 1 evict_first, 2 evict_last
     // reduce outputs
     float* coords;
@@ -253,9 +255,14 @@ static int pick_cluster(int op, long long n_vol, long long vol_bytes, int NR) {
 template <typename T, bool kTma, int kOp>
 static int launch_stream(const Params& p, int S, cudaStream_t st) {
     auto kern = k_stream<T, kTma, kOp>;
-    const size_t smem = sizeof(SmemLayout) + (kTma ? (size_t)kStages * kStageBytes : 0);
+    size_t smem = sizeof(SmemLayout) + (kTma ? (size_t)kStages * kStageBytes : 0);
+    if (const char* e = getenv("HIPE_PAD_SMEM")) smem += (size_t)atoi(e);   // tuning: lowers CTAs/SM
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
+    if (S > 8) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e != cudaSuccess) return (int)e;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(p.n_vol * S), 1, 1);
     cfg.blockDim = dim3(kTma ? kConsumers + 32 : kConsumers, 1, 1);
@@ -304,12 +311,26 @@ static int dispatch(Params p, int cluster, int variant, cudaStream_t st) {
     p.G = (int)(row_b / 16);
     p.R = kConsumers / p.G;
     int S = cluster ? cluster : pick_cluster(kOp, p.n_vol, p.vol_bytes, p.NR);
+    const bool tma_ = (variant == HIPE_VARIANT_AUTO) ? true : (variant == HIPE_VARIANT_TMA);
+    const long long ring_rows = (long long)kStages * kPasses * p.R;   // rows one CTA's ring holds
+    if (kOp == OP_FUSED && tma_ && !cluster && getenv("HIPE_RESIDENT")) {
+        // smallest cluster whose CTAs keep their whole share in the shared-memory ring: the
+        // second pass then re-reads shared memory, and HBM sees exactly one read + one write.
+        // Opt-in only: measured on B200 it is SLOWER than re-reading through L2 (64^3 fp32:
+        // 0.81 ms at S=16 vs 0.57 ms at S=4) because 64 KB CTAs are too short-lived to hide the
+        // cluster launch + barrier latency; the persistent form is the one that pays.
+        for (int c = 1; c <= kMaxCluster; c *= 2)
+            if ((p.NR + c - 1) / c <= ring_rows && p.NR >= c) { S = c; break; }
+    }
     while (S > 1 && p.NR < S) S /= 2;
+    p.resident = (kOp == OP_FUSED && tma_ && (p.NR + S - 1) / S <= ring_rows) ? 1 : 0;
     const bool tma = (variant == HIPE_VARIANT_AUTO) ? true : (variant == HIPE_VARIANT_TMA);
     // two adjacent vectors per visit in the reduce pass when rows are 32-byte multiples (shared
     // memory reads only: from global memory it would fetch every 32-byte sector twice)
     p.nv2 = (tma && p.G % 2 == 0) ? 1 : 0;
     if (const char* e = getenv("HIPE_NV2")) p.nv2 = (p.nv2 && e[0] != '0') ? 1 : 0;
+    p.st_hint = 0;
+    if (const char* e = getenv("HIPE_ST_HINT")) p.st_hint = (e[0] != '0') ? 1 : 0;
     return tma ? launch_stream<T, true, kOp>(p, S, st) : launch_stream<T, false, kOp>(p, S, st);
 }
 
@@ -319,7 +340,7 @@ static int check_geom(const void* in, int dtype, long long n_vol, int D, int H, 
     if (n_vol < 0 || D <= 0 || H <= 0 || W <= 0) return HIPE_E_SHAPE;
     if ((long long)D * H * W > (1ll << 31)) return HIPE_E_SHAPE;
     if (n_vol * kMaxCluster > 0x7fffffffll) return HIPE_E_SHAPE;
-    if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8) return HIPE_E_CLUSTER;
+    if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8 && cluster != 16) return HIPE_E_CLUSTER;
     if (variant < 0 || variant > 2) return HIPE_E_SHAPE;
     const int esz = dtype == HIPE_F32 ? 4 : 2;
     if (reinterpret_cast<uintptr_t>(in) % esz) return HIPE_E_ALIGN;

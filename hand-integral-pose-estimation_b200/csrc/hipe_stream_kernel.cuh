@@ -300,6 +300,7 @@ __device__ __forceinline__ void write_pass(const Params& p, const Tile& t, unsig
     using V16 = Vec16<T>;
     constexpr int VEC = V16::N;
     const int lane = tid & 31;
+    const bool resident = kTma && p.resident;
     const bool active = tid < p.G * p.R;
     const int cg = active ? tid % p.G : 0;
     const int rr = active ? tid / p.G : 0;
@@ -327,6 +328,7 @@ __device__ __forceinline__ void write_pass(const Params& p, const Tile& t, unsig
 #pragma unroll
         for (int j = 0; j < VEC; ++j) ax[j] = kx * (float)((double)(x0i + j) - Ex);
     }
+    const uint64_t st_pol = policy_evict_first();
     float yf = (float)(row_first % p.H), zf = (float)(row_first / p.H);
     const float dyf = (float)(p.R % p.H), dzf = (float)(p.R / p.H), Hf = (float)p.H;
 
@@ -334,9 +336,13 @@ __device__ __forceinline__ void write_pass(const Params& p, const Tile& t, unsig
         float v[kPasses][VEC];
         uint32_t sbase = 0;
         if constexpr (kTma) {
-            const int slot = it % kStages;
-            mbar_wait(smem_u32(&sm.full[slot]), (it / kStages) & 1);
-            sbase = lds_base + slot * kStageBytes;
+            if (resident) {
+                sbase = lds_base + i * kStageBytes;   // stage i still sits in slot i: no reload, no wait
+            } else {
+                const int slot = it % kStages;
+                mbar_wait(smem_u32(&sm.full[slot]), (it / kStages) & 1);
+                sbase = lds_base + slot * kStageBytes;
+            }
         }
         const bool whole = i < full;
 #pragma unroll
@@ -349,8 +355,10 @@ __device__ __forceinline__ void write_pass(const Params& p, const Tile& t, unsig
             }
         }
         if constexpr (kTma) {
-            __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&sm.empty[it % kStages]));
+            if (!resident) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&sm.empty[it % kStages]));
+            }
         }
 #pragma unroll
         for (int q = 0; q < kPasses; ++q) {
@@ -363,7 +371,10 @@ __device__ __forceinline__ void write_pass(const Params& p, const Tile& t, unsig
                     const float e = ex2(fmaf(v[q][j], kLog2e, -ML));
                     o[j] = e * (ax[j] + rowterm);
                 }
-                stg_stream(gdst + (long long)(i * kPasses + q) * pass_bytes, V16::pack(o));
+                if (p.st_hint)
+                    stg_stream_hint(gdst + (long long)(i * kPasses + q) * pass_bytes, V16::pack(o), st_pol);
+                else
+                    stg_stream(gdst + (long long)(i * kPasses + q) * pass_bytes, V16::pack(o));
             }
             yf += dyf;
             zf += dzf;
@@ -426,7 +437,7 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
                 const uint64_t pn = policy_evict_normal(), pf = policy_evict_first(), pl = policy_evict_last();
                 const uint64_t pol_a = p.pol1 == 0 ? pn : (p.pol1 == 1 ? pf : pl);
                 const uint64_t pol_b = p.pol2 == 0 ? pn : (p.pol2 == 1 ? pf : pl);
-                const int total = t.nst * kNumPassesOverVolume;
+                const int total = t.nst * (p.resident ? 1 : kNumPassesOverVolume);
                 for (int it = 0; it < total; ++it) {
                     const int slot = it % kStages;
                     const int i = (it >= t.nst) ? it - t.nst : it;

@@ -41,7 +41,7 @@ extern "C" {
 #define HIPE_E_SHAPE (-2)    /* non-positive / overflowing dimension                  */
 #define HIPE_E_ALIGN (-3)    /* pointer not aligned to its element size               */
 #define HIPE_E_NULL (-4)     /* required pointer is NULL                              */
-#define HIPE_E_CLUSTER (-5)  /* cluster size not in {0,1,2,4,8}                       */
+#define HIPE_E_CLUSTER (-5)  /* cluster size not in {0,1,2,4,8,16}                    */
 #define HIPE_E_ARCH (-6)     /* current device is not compute capability 10.x         */
 
 /* variant selector for the streaming kernels (0 = library default) */
@@ -65,7 +65,7 @@ HIPE_API const char* hipe_strerror(int code);
  *                resolution at E ~ 32
  *   stats_dev  : n_vol*2 floats  (max logit, sum exp(logit-max)); input of the backward
  *                (nullable; written as (0, sum) when apply_softmax == 0)
- *   cluster    : CTAs cooperating on one volume: 0 = auto, else 1|2|4|8
+ *   cluster    : CTAs cooperating on one volume: 0 = auto, else 1|2|4|8|16
  *   variant    : HIPE_VARIANT_*
  */
 HIPE_API int hipe_softargmax_fwd(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,

@@ -32,7 +32,7 @@ def main():
     ap.add_argument("--B", type=int, default=64)
     ap.add_argument("--dim", type=int, default=64)
     ap.add_argument("--dtype", default="f32")
-    ap.add_argument("--clusters", default="1,2,4,8")
+    ap.add_argument("--clusters", default="0,1,2,4,8")
     ap.add_argument("--variants", default="1,2")
     ap.add_argument("--ops", default="fwd,bwd,fused")
     a = ap.parse_args()

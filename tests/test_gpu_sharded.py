@@ -1,0 +1,63 @@
+"""GPU, world_size 2 over NCCL (skipped on a 1-GPU box): the batch-sharded criterion with the real
+kernels on each rank against the single-process oracle semantics."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+J, D = 21, 16
+
+
+def _worker(rank, world, port, B, out_dir):
+    import torch.distributed as dist
+    from hipe_b200 import parallel as PL
+    from tests import synth
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        hm = synth.heatmaps(B, J, D, D, D, "peaked", seed=42)
+        gt, vis = synth.targets(B, J, seed=42, zero_vis_frac=0.1)
+        lo, hi = PL.shard_bounds(B, world, rank)
+        x = torch.as_tensor(hm[lo:hi]).cuda().requires_grad_(True)
+        crit = PL.ShardedJointLocationLoss(global_batch=B)
+        loss = crit(x, torch.as_tensor(gt[lo:hi]).cuda(), torch.as_tensor(vis[lo:hi]).cuda())
+        loss.backward()
+        X, Y = synth.procrustes_pairs(101, seed=4)
+        l2, h2 = PL.shard_bounds(101, world, rank)
+        pa, raw = PL.sharded_pa_mpjpe(X[l2:h2], Y[l2:h2])
+        np.savez(os.path.join(out_dir, "r%d.npz" % rank), loss=loss.item(), coords=crit.coords.cpu().numpy(),
+                 grad=x.grad.cpu().numpy(), pa=pa.item(), raw=raw.item())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_sharded_criterion_nccl_world2(tmp_path):
+    import torch.multiprocessing as mp
+    from oracle import integral_np as O
+    from oracle import procrustes_np as P
+    from tests import synth
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    B, world = 6, 2
+    mp.spawn(_worker, args=(world, port, B, str(tmp_path)), nprocs=world, join=True)
+    hm = synth.heatmaps(B, J, D, D, D, "peaked", seed=42).astype(np.float64)
+    gt, vis = synth.targets(B, J, seed=42, zero_vis_frac=0.1)
+    ref_loss, ref_c = O.joint_location_loss(hm, gt, vis, return_coords=True)      # equal shards: global sum / B
+    ref_g = O.joint_location_loss_grad(hm, gt, vis)
+    outs = [np.load(os.path.join(str(tmp_path), "r%d.npz" % r)) for r in range(world)]
+    assert outs[0]["loss"] == outs[1]["loss"]
+    assert abs(outs[0]["loss"] - ref_loss) <= 1e-5 * ref_loss
+    for r in range(world):
+        np.testing.assert_array_equal(outs[r]["coords"], outs[0]["coords"])
+        err = np.abs(outs[r]["coords"] - ref_c)
+        assert (err <= 1e-5 * np.maximum(np.abs(ref_c), 0.5)).all()
+        g = outs[r]["grad"].reshape(-1, D ** 3)
+        rg = ref_g[r * 3:(r + 1) * 3].reshape(-1, D ** 3)
+        assert (np.abs(g - rg) <= 1e-5 * np.abs(rg).max(axis=1, keepdims=True) + 1e-12).all()
+    X, Y = synth.procrustes_pairs(101, seed=4)
+    rpa, rraw = P.pa_mpjpe(X, Y)
+    assert abs(outs[0]["pa"] - rpa) < 1e-9 and abs(outs[1]["raw"] - rraw) < 1e-9
