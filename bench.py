@@ -262,11 +262,12 @@ def run_ours(a):
     traffic = None
     try:
         prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic = prof.get("fused" if a.fused else "softargmax_bwd", {}).get("%s_%d_B%d" % (a.dtype, D, B))
+        traffic = prof.get(("resident" if "joint_loss_resident" in kern else "fused") if a.fused else "softargmax_bwd", {}).get("%s_%d_B%d" % (a.dtype, D, B))
     except Exception:
         pass
     if a.fused:
-        dom, per_vol = "joint_loss_fused", 2 * V * esz           # one HBM read + one write per volume
+        dom = "joint_loss_resident" if "joint_loss_resident" in kern else "joint_loss_fused"
+        per_vol = 2 * V * esz                                    # one HBM read + one write per volume
     else:
         dom, per_vol = "softargmax_bwd", 2 * V * esz             # read V, write V
     dom_ms = kern.get(dom)

@@ -7,7 +7,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(os.path.dirname(HERE), "csrc")
 LIB_PATH = os.path.join(HERE, "libhipe_b200.so")
-SOURCES = ["hipe_softargmax.cu", "hipe_eval.cu", "hipe_host.cu"]
+SOURCES = ["hipe_softargmax.cu", "hipe_resident.cu", "hipe_eval.cu", "hipe_host.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--use_fast_math=false",
@@ -27,6 +27,7 @@ def needs_build():
     t = os.path.getmtime(LIB_PATH)
     deps = [os.path.join(CSRC, s) for s in SOURCES] + [
         os.path.join(CSRC, "hipe_common.cuh"),
+        os.path.join(CSRC, "hipe_stream_kernel.cuh"),
         os.path.join(os.path.dirname(os.path.dirname(HERE)), "include", "hipe_b200.h"),
     ]
     return any(os.path.getmtime(d) > t for d in deps)

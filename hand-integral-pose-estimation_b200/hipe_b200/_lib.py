@@ -9,6 +9,7 @@ import threading
 from . import _build
 
 F32, BF16, F64 = 0, 1, 3
+E_UNSUPPORTED = -7
 VARIANT_AUTO, VARIANT_TMA, VARIANT_LDG = 0, 1, 2
 
 _c = ctypes
@@ -24,6 +25,9 @@ SIGNATURES = {
     "hipe_l1_loss_fwd": (_i, [_vp, _vp, _vp, _i, _ll, _i, _d, _vp, _vp, _vp]),
     "hipe_joint_loss_fused": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp,
                                    _i, _i, _vp]),
+    "hipe_resident_workspace_bytes": (_ll, [_i, _ll, _i, _i, _i]),
+    "hipe_joint_loss_resident": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp,
+                                      _vp, _ll, _vp]),
     "hipe_scale_inplace": (_i, [_vp, _i, _ll, _vp, _vp]),
     "hipe_sum_f64": (_i, [_vp, _ll, _d, _vp, _vp]),
     "hipe_procrustes_batched": (_i, [_vp, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -162,9 +162,75 @@ def sum_f64(x, scale=1.0):
     return out
 
 
-def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, variant=None):
+# "auto": the persistent on-chip launch whenever the geometry allows it, else the L2 re-read launch
+FUSED_MODE = "auto"          # "auto" | "resident" | "stream"
+_WORKSPACES = {}             # (device index, stream) -> uint8 scratch tensor, grown on demand
+
+
+def resident_supported(logits, n_vol, D, H, W):
+    return _lib.load().hipe_resident_workspace_bytes(_logits_code(logits), n_vol, D, H, W) > 0
+
+
+def _workspace(dev, nbytes):
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _WORKSPACES.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty((nbytes + 255) // 256 * 256, dtype=torch.uint8, device=dev)
+        _WORKSPACES[key] = ws
+    return ws
+
+
+def resident_timed_out(device, n_vol):
+    """True if an inter-CTA wait of the last resident launch on this device/stream hit its spin
+    limit (word [n_vol] of the workspace).  Synchronises; for tests and diagnostics."""
+    dev = torch.device(device)
+    ws = _WORKSPACES.get((dev.index, torch.cuda.current_stream(dev).cuda_stream))
+    if ws is None:
+        return False
+    return bool(ws[4 * n_vol:4 * n_vol + 4].view(torch.int32).item() != 0)
+
+
+def joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm):
+    """hipe_joint_loss_resident: same outputs as joint_loss_fused, each volume read from HBM once."""
+    _need_cuda(logits, "heatmaps")
+    code = _logits_code(logits)
+    if not logits.is_contiguous():
+        logits = logits.contiguous()
+    dev = logits.device
+    lib = _lib.load()
+    need = lib.hipe_resident_workspace_bytes(code, n_vol, D, H, W)
+    if need <= 0:
+        raise _lib.HipeError("libhipe_b200: error %d: geometry not supported by the resident launch"
+                             % _lib.E_UNSUPPORTED)
+    coords = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
+    gt, vis, tcode, _ = _targets(coords, gt, vis)
+    if gt.numel() != n_vol * 3 or vis.numel() != n_vol * 3:
+        raise ValueError("targets must hold 3 values per volume")
+    expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev)
+    stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
+    terms = torch.empty((n_vol * 3,), dtype=torch.float64, device=dev)
+    dlogits = torch.empty_like(logits)
+    with torch.cuda.device(dev):
+        ws = _workspace(dev, need)
+        with _launch("joint_loss_resident", logits):
+            check(lib.hipe_joint_loss_resident(
+                logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
+                coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), dlogits.data_ptr(),
+                ws.data_ptr(), ws.numel(), _stream(logits)))
+    return coords, expect, stats, terms, dlogits
+
+
+def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, variant=None, mode=None):
     """One launch: coords, expect, stats, per-coordinate loss terms (n_vol*3 fp64), dlogits."""
     _need_cuda(logits, "heatmaps")
+    mode = FUSED_MODE if mode is None else mode
+    if mode == "resident" or (mode == "auto" and cluster is None and variant is None
+                              and resident_supported(logits, n_vol, D, H, W)):
+        try:
+            return joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm)
+        except _lib.HipeError as e:
+            if mode == "resident" or "error %d:" % _lib.E_UNSUPPORTED not in str(e):
+                raise
     code = _logits_code(logits)
     if not logits.is_contiguous():
         logits = logits.contiguous()

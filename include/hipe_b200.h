@@ -43,6 +43,7 @@ extern "C" {
 #define HIPE_E_NULL (-4)     /* required pointer is NULL                              */
 #define HIPE_E_CLUSTER (-5)  /* cluster size not in {0,1,2,4,8,16}                    */
 #define HIPE_E_ARCH (-6)     /* current device is not compute capability 10.x         */
+#define HIPE_E_UNSUPPORTED (-7) /* this entry point cannot take the geometry / launch: use the general one */
 
 /* variant selector for the streaming kernels (0 = library default) */
 #define HIPE_VARIANT_AUTO 0
@@ -117,6 +118,27 @@ HIPE_API int hipe_joint_loss_fused(const void* logits_dev, int dtype, long long 
                           float* coords_dev, double* expect_dev, float* stats_dev,
                           double* loss_terms_dev /* n_vol*3 */, void* dlogits_dev,
                           int cluster, int variant, void* stream);
+
+/*
+ * The same contract as hipe_joint_loss_fused, as ONE persistent cooperative launch that keeps
+ * every volume on chip between the reduction and the gradient write: HBM sees each volume once
+ * in and its gradient once out (V*s + V*g bytes per volume instead of 2*V*s + V*g).  A volume is
+ * cut into items of <= 128 KB taken by different CTAs (one CTA per SM, 13 x 16 KB TMA ring);
+ * the items' partial sums are merged through `workspace_dev`.
+ *   workspace_dev   : caller-owned device scratch, 256-byte aligned, of at least
+ *                     hipe_resident_workspace_bytes(...) bytes; holds nothing between calls.
+ *                     Word [n_vol] (uint32) is set non-zero if an inter-CTA wait ever timed out.
+ * Returns HIPE_E_UNSUPPORTED when the geometry cannot be tiled for it (rows not a multiple of
+ * 16 bytes, stage rows neither dividing nor a multiple of H, ...) or the grid cannot be made
+ * co-resident; callers then use hipe_joint_loss_fused.  hipe_resident_workspace_bytes returns 0
+ * in exactly the geometry cases.
+ */
+HIPE_API long long hipe_resident_workspace_bytes(int dtype, long long n_vol, int D, int H, int W);
+HIPE_API int hipe_joint_loss_resident(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
+                             const void* gt_dev, const void* vis_dev, int tgt_dtype, double norm,
+                             float* coords_dev, double* expect_dev, float* stats_dev,
+                             double* loss_terms_dev /* n_vol*3 */, void* dlogits_dev,
+                             void* workspace_dev, long long workspace_bytes, void* stream);
 
 /*
  * x[i] *= *gscale_dev for n elements of `dtype`, in place; returns without touching memory when

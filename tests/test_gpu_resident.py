@@ -1,0 +1,164 @@
+"""GPU parity of the persistent on-chip fused launch (hipe_joint_loss_resident) against the oracle,
+and its agreement with the two-launch path.  Same gates as tests/test_gpu_parity.py."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import integral_np as O
+from tests import synth
+
+pytestmark = pytest.mark.gpu
+
+# geometry -> items per volume the tiling gives (P); None = not tileable, must report unsupported
+RES_GEOMS = {
+    (16, 16, 16): 1,     # stage = 8 z-slices, half the consumers idle
+    (32, 32, 32): 1,
+    (64, 64, 64): 8,     # headline: stage == one z-slice
+    (56, 56, 56): 7,     # reference default (main/config.py:23-25): 14 rows per visit
+    (96, 96, 96): 36,    # BASELINE configs[3]: stage = a third of a z-slice
+    (16, 128, 64): 4,    # stage = half a z-slice (SR | H, non-zero y base)
+    (12, 20, 24): 1,     # 30 rows per visit, 180 of 256 consumers active
+}
+UNSUPPORTED = [(8, 8, 8), (5, 6, 7), (3, 9, 100)]
+
+
+def _cuda(a, dtype=None):
+    t = torch.as_tensor(a).cuda()
+    return t if dtype is None else t.to(dtype)
+
+
+def _check(hm, gt, vis, D, H, W, B, J, out, tgt=np.float64):
+    coords, expect, stats, terms, dlogits = out
+    h64 = hm.astype(np.float64)
+    ref_loss, ref_c = O.joint_location_loss(h64, gt.astype(np.float64), vis.astype(np.float64), return_coords=True)
+    ref_g = O.joint_location_loss_grad(h64, gt.astype(np.float64), vis.astype(np.float64))
+    c = coords.view(B, 3 * J).cpu().numpy().astype(np.float64)
+    assert (np.abs(c - ref_c) <= 1e-5 * np.maximum(np.abs(ref_c), 0.5)).all(), np.abs(c - ref_c).max()
+    loss = terms.sum().item() / B
+    assert abs(loss - ref_loss) <= 1e-5 * abs(ref_loss), (loss, ref_loss)
+    d = dlogits.float().cpu().numpy().astype(np.float64).reshape(B * J, -1)
+    r = ref_g.reshape(B * J, -1)
+    c_close = (np.abs(ref_c - gt.astype(np.float64)) < 1e-5).reshape(B * J, 3).any(axis=1)
+    scale = np.abs(r).max(axis=1, keepdims=True)
+    rel = np.abs(d - r) / (scale + 1e-300)
+    ok = (np.abs(d - r) <= 1e-5 * scale + 1e-12).all(axis=1) | c_close
+    assert ok.all(), "worst relative gradient error %.3e" % rel[~c_close].max()
+    # stats: (max, sum exp) per volume
+    v = h64.reshape(B * J, -1)
+    m = v.max(axis=1)
+    np.testing.assert_allclose(stats[:, 0].cpu().numpy(), m, rtol=0, atol=0)
+    np.testing.assert_allclose(stats[:, 1].cpu().numpy(), np.exp(v - m[:, None]).sum(axis=1), rtol=2e-6)
+    return rel.max()
+
+
+@pytest.mark.parametrize("regime", ["noise", "peaked", "sharp"])
+@pytest.mark.parametrize("geom", list(RES_GEOMS))
+def test_resident_vs_oracle(geom, regime):
+    from hipe_b200 import ops
+    D, H, W = geom
+    J, B = 21, 2
+    hm = synth.heatmaps(B, J, D, H, W, regime, seed=11)
+    gt, vis = synth.targets(B, J, seed=11, zero_vis_frac=0.1)
+    x = _cuda(hm)
+    assert ops.resident_supported(x, B * J, D, H, W)
+    out = ops.joint_loss_resident(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    torch.cuda.synchronize()
+    assert not ops.resident_timed_out(x.device, B * J)
+    _check(hm, gt, vis, D, H, W, B, J, out)
+
+
+@pytest.mark.parametrize("geom", UNSUPPORTED)
+def test_unsupported_geometries_fall_back(geom):
+    from hipe_b200 import _lib, ops
+    D, H, W = geom
+    J, B = 21, 2
+    hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=3)
+    gt, vis = synth.targets(B, J, seed=3)
+    x = _cuda(hm)
+    assert not ops.resident_supported(x, B * J, D, H, W)
+    with pytest.raises(_lib.HipeError):
+        ops.joint_loss_resident(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    # "auto" silently takes the L2 re-read launch (still a CUDA kernel of this library)
+    out = ops.joint_loss_fused(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    _check(hm, gt, vis, D, H, W, B, J, out)
+
+
+def test_many_items_per_cta_and_straddling_rounds():
+    """More items than CTAs (each CTA loops, the pipeline's head/tail split is exercised) with a
+    volume count that makes item rounds straddle volumes (148 is not a multiple of 8)."""
+    from hipe_b200 import ops
+    D = H = W = 64
+    J, B = 21, 5             # 105 volumes x 8 items = 840 items over 148 CTAs
+    hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=21)
+    gt, vis = synth.targets(B, J, seed=21)
+    x = _cuda(hm)
+    out = ops.joint_loss_resident(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    torch.cuda.synchronize()
+    assert not ops.resident_timed_out(x.device, B * J)
+    _check(hm, gt, vis, D, H, W, B, J, out)
+    # bit-reproducible: a second launch gives identical bytes (fixed merge order)
+    out2 = ops.joint_loss_resident(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    assert torch.equal(out[4], out2[4]) and torch.equal(out[0], out2[0]) and torch.equal(out[3], out2[3])
+
+
+def test_resident_agrees_with_two_launch_path():
+    from hipe_b200 import ops
+    D = H = W = 64
+    J, B = 21, 3
+    hm = synth.heatmaps(B, J, D, H, W, "sharp", seed=5)
+    gt, vis = synth.targets(B, J, seed=5)
+    x = _cuda(hm)
+    c1, e1, s1, t1, d1 = ops.joint_loss_resident(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    c0, e0, s0 = ops.softargmax_forward(x, B * J, D, H, W)
+    _, g = ops.l1_loss(c0.view(B, 3 * J), _cuda(gt), _cuda(vis), 1.0 / B)
+    d0 = ops.softargmax_backward(x, B * J, D, H, W, s0, e0, g.view(-1, 3))
+    assert (c1 - c0).abs().max().item() <= 2e-7
+    assert (e1 - e0).abs().max().item() <= 1e-5          # voxel units
+    same_sign = ((c1 - _cuda(gt).view(-1, 3)).sign() == (c0 - _cuda(gt).view(-1, 3)).sign()).all(dim=1)
+    scale = d0.view(B * J, -1).abs().amax(dim=1, keepdim=True)
+    rel = ((d1 - d0).view(B * J, -1).abs() / scale)[same_sign]
+    assert rel.max().item() <= 2e-5
+
+
+def test_resident_bf16():
+    from hipe_b200 import ops
+    D = H = W = 64
+    J, B = 21, 2
+    hm32 = synth.heatmaps(B, J, D, H, W, "peaked", seed=4)
+    gt, vis = synth.targets(B, J, seed=4)
+    xb = _cuda(hm32).to(torch.bfloat16)
+    up = xb.float().cpu().numpy().astype(np.float64)       # the rounded tensor is the oracle's input
+    assert ops.resident_supported(xb, B * J, D, H, W)
+    coords, expect, stats, terms, d = ops.joint_loss_resident(xb, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    ref_loss, ref_c = O.joint_location_loss(up, gt, vis, return_coords=True)
+    c = coords.view(B, 3 * J).cpu().numpy().astype(np.float64)
+    assert (np.abs(c - ref_c) <= 1e-5 * np.maximum(np.abs(ref_c), 0.5)).all()
+    assert abs(terms.sum().item() / B - ref_loss) <= 1e-5 * abs(ref_loss)
+    refg = O.joint_location_loss_grad(up, gt, vis)
+    want = torch.as_tensor(refg).to(torch.bfloat16).float().numpy().reshape(B * J, -1)
+    got = d.float().cpu().numpy().reshape(B * J, -1)
+    ulp = np.maximum(np.abs(want), 1e-30) * 2.0 ** -7
+    c_close = (np.abs(ref_c - gt) < 1e-5).reshape(B * J, 3).any(axis=1)
+    ok = (np.abs(got - want) <= ulp + 1e-12).all(axis=1) | c_close
+    assert ok.all()
+
+
+def test_module_uses_resident_launch_and_scales_upstream_gradient():
+    from hipe_b200 import ops
+    from nets import loss as L
+    D = H = W = 32
+    J, B = 21, 2
+    hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=9)
+    gt, vis = synth.targets(B, J, seed=9)
+    ops.KERNEL_EVENTS = {}
+    try:
+        x = _cuda(hm).requires_grad_(True)
+        loss = L.JointLocationLoss(fused=True)(x, _cuda(gt), _cuda(vis))
+        (loss * 0.25).backward()
+        assert "joint_loss_resident" in ops.KERNEL_EVENTS
+    finally:
+        ops.KERNEL_EVENTS = None
+    y = _cuda(hm).requires_grad_(True)
+    L.JointLocationLoss()(y, _cuda(gt), _cuda(vis)).backward()
+    scale = y.grad.view(B * J, -1).abs().amax(dim=1, keepdim=True)
+    assert ((x.grad - 0.25 * y.grad).view(B * J, -1).abs() <= 2e-5 * 0.25 * scale + 1e-12).all()
