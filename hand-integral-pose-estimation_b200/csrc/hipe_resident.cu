@@ -7,29 +7,32 @@
 // the reduction and the gradient write.
 //
 // A 64^3 fp32 volume is 1 MiB, more than one SM's shared memory, so a volume is cut into P
-// ITEMS of <= 8 stages (a stage = SR whole rows <= 16 KB) and the items of one volume are
+// ITEMS of <= 4 stages (a stage = SR whole rows <= 16 KB) and the items of one volume are
 // taken by P different CTAs of a persistent grid (one CTA per SM, cooperative launch so that
 // all of them are co-resident).  Per CTA:
 //
 //   producer warp   streams the CTA's items, stage by stage, into a 13-slot x 16 KB ring with
 //                   1-D TMA bulk copies (evict_first: HBM lines are never needed again);
-//   256 consumers   REDUCE a stage: online-max softmax; the exponentials are written back over
-//                   the logits in the ring slot ("stash", fp32 only) together with the offset
+//   reduce team     (256 threads) REDUCE a stage: online-max softmax; the exponentials are
+//                   written back over the logits in the ring slot ("stash", fp32 only) together with the offset
 //                   they are relative to, so the gradient pass needs no second MUFU.EX2;
 //                   per-thread fp32 accumulators per owned (row-in-stage, column) position;
 //                   PUBLISH the item's partial sums to a global workspace and bump the
 //                   volume's arrival counter (release);
+//   write team      (256 threads)
 //                   WAIT until the counter shows all P partials (acquire), merge them in a
 //                   fixed order (every CTA of the volume computes bit-identical scalars), form
 //                   the L1 gradient sign(c-gt)*vis*norm (loss.py:86-89);
 //                   WRITE: dlogits = e*2^(off-M)/L * (gx(x-Ex)/W + gy(y-Ey)/H + gz(z-Ez)/D)
 //                   from the stashed ring slot, then release the slot to the producer.
 //
-// Software pipeline: the first (13 - n) stages of the NEXT item are reduced between PUBLISH
-// and WAIT of the current one, so the cross-CTA latency (global flag round trip, ~1 us) is
-// covered by useful work and the ring always has loads in flight.  No CTA ever waits before
-// it has published, and waits only point at volumes with a smaller or equal index: with all
-// CTAs co-resident the schedule cannot deadlock.
+// REDUCE/PUBLISH and WAIT/WRITE are done by two different 256-thread teams of the CTA working
+// on consecutive items through the same ring: the reduce team runs up to (13 - n) stages (2-3 items) ahead
+// of the write team, so the cross-CTA latency (global flag round trip, ~1 us) and each team's
+// per-item serial work are covered by the other team's streaming and the ring always has loads
+// in flight.  A reduce team never waits on another CTA, a write team only waits on volumes
+// whose items were all published by reduce teams that needed strictly earlier volumes to
+// drain: with all CTAs co-resident (cooperative launch) the schedule cannot deadlock.
 //
 // Precision (same contract as hipe_stream_kernel.cuh): exponentials are fp32; each expectation
 // is a ratio of fp64 sums built from the SAME rounded fp32 atoms, so rounding only re-weights
@@ -49,8 +52,9 @@ constexpr int kNW = kC / 32;          // consumer warps
 constexpr int kSlots = 13;            // ring depth
 constexpr int kSlotBytes = 16384;     // ring slot
 constexpr int kKP = 4;                // 16-byte vectors per thread per stage
-constexpr int kMaxItemStages = 8;     // an item never exceeds 8 stages (128 KB)
-constexpr int kMaxRtRows = 1024;      // rows of one item (<= 8 stages x 128 rows)
+constexpr int kMaxItemStages = 4;     // an item never exceeds 4 stages (64 KB): >= 2 whole items of look-ahead in the ring
+constexpr int kRD = 16;               // reduce->write hand-off barriers (the ring never holds more than 13 items)
+constexpr int kMaxRtRows = 1024;      // rows of one item (<= 4 stages x 256 rows)
 constexpr int kNSums = 7;             // S0c Sx Syo Szo S0t Syb Szb
 constexpr unsigned kSpinLimit = 1u << 22;
 
@@ -90,11 +94,12 @@ struct Smem {
     float rt[kMaxRtRows];         // per-row gradient term of the item being written
     unsigned long long full[kSlots];
     unsigned long long empty[kSlots];
-    double wred[kNW][8];
+    unsigned long long red_done[kRD];  // reduce team -> write team: every stage of the item is stashed
+    double wred[kNW][8];          // reduce team scratch
     float wmax[kNW];
-    double finE[3];               // Ex, Ey, Ez
-    double finL;                  // sum exp
-    float fin[4];                 // M, gx, gy, gz
+    double finE[3];               // write team: Ex, Ey, Ez
+    double finK[3];               //             g_a / dim_a / L per axis
+    float finM;                   //             volume maximum
 };
 
 struct Item {
@@ -113,8 +118,9 @@ __device__ __forceinline__ Item decode(const Params& p, long long w) {
     return it;
 }
 
-__device__ __forceinline__ void consumer_barrier() {
-    asm volatile("bar.sync 1, %0;" ::"n"(kC) : "memory");
+template <int kId>
+__device__ __forceinline__ void team_barrier() {
+    asm volatile("bar.sync %0, %1;" ::"n"(kId), "n"(kC) : "memory");
 }
 
 // mbarrier wait that traps instead of hanging the GPU if the pipeline logic is ever wrong
@@ -151,46 +157,36 @@ __device__ __forceinline__ float rebase_w(float m_from, float m_to) {
     return (m_from == kNegInf) ? 0.f : ex2(__fsub_rn(__fmul_rn(m_from, kLog2e), __fmul_rn(m_to, kLog2e)));
 }
 
-// per-thread reduction state of the item being reduced
-template <int VEC>
-struct RState {
-    float m, mL;
-    float c[kKP][VEC];
-    double s0t, syb, szb;
-    __device__ __forceinline__ void init() {
-        m = kNegInf;
-        mL = kNegInf;
-#pragma unroll
-        for (int q = 0; q < kKP; ++q)
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) c[q][j] = 0.f;
-        s0t = syb = szb = 0.0;
-    }
-};
-
+// Thread roles inside the CTA (kThreads = 2*kC + 32):
+//   [0, kC)        REDUCE team: online softmax + stash + publish of item k+1
+//   [kC, 2kC)      WRITE team : flag wait + scalars + gradient write of item k, releases slots
+//   [2kC, 2kC+32)  producer warp (one elected lane)
+// The reduce team runs at most 13 - n stages ahead of the write team (ring capacity), which is
+// what hides the cross-CTA flag latency and the per-item serial work of either team.
 template <typename T, bool kStash>
-__global__ void __launch_bounds__(kC + 32, 1) k_resident(const Params p) {
+__global__ void __launch_bounds__(2 * kC + 32, 1) k_resident(const Params p) {
     using V16 = Vec16<T>;
     constexpr int VEC = V16::N;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kSlots * kSlotBytes);
-    const int tid = threadIdx.x;
     const uint32_t ring = smem_u32(smem_raw);
 
-    if (tid == 0) {
+    if (threadIdx.x == 0) {
 #pragma unroll
         for (int s = 0; s < kSlots; ++s) {
             mbar_init(smem_u32(&sm.full[s]), 1);
             mbar_init(smem_u32(&sm.empty[s]), kNW);
         }
+#pragma unroll
+        for (int s = 0; s < kRD; ++s) mbar_init(smem_u32(&sm.red_done[s]), kNW);
         mbar_fence_init();
         fence_proxy_async();
     }
     __syncthreads();
 
-    if (tid >= kC) {
+    if (threadIdx.x >= 2 * kC) {
         // ------------------------------ producer warp ------------------------------
-        if (tid == kC) {
+        if (threadIdx.x == 2 * kC) {
             const uint64_t pol = policy_evict_first();
             unsigned g = 0;
             for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x) {
@@ -209,162 +205,179 @@ __global__ void __launch_bounds__(kC + 32, 1) k_resident(const Params p) {
         return;
     }
 
-    // --------------------------------- consumers ---------------------------------
+    const bool is_writer = threadIdx.x >= kC;
+    const int tid = is_writer ? threadIdx.x - kC : threadIdx.x;   // team-local
     const int lane = tid & 31, warp = tid >> 5;
     const bool active = tid < p.nact;
     const int cg = active ? tid % p.G : 0;
     const int rr = active ? tid / p.G : 0;
     const int x0 = cg * VEC;
     const uint32_t lds_base = ring + 16u * tid;
-    const float Hf = (float)p.H;
-    (void)Hf;
 
-    unsigned g_red = 0, g_wr = 0;   // global stage counters of the reduce / write sequences
-    RState<VEC> st;
-
-    // ---- reduce stages [s_begin, s_end) of `it` ----
-    auto reduce_stages = [&](const Item& it, int s_begin, int s_end) {
-        for (int s = s_begin; s < s_end; ++s, ++g_red) {
-            const unsigned slot = g_red % kSlots;
-            mbar_wait_bounded(smem_u32(&sm.full[slot]), (g_red / kSlots) & 1);
-            if (!active) continue;
-            const uint32_t sbase = lds_base + slot * kSlotBytes;
-            float v[kKP][VEC];
+    if (!is_writer) {
+        // =============================== REDUCE team ===============================
+        unsigned g = 0, item_no = 0;
+        // row offsets of this thread's kKP visits inside a stage
+        int yo[kKP], zo[kKP];
 #pragma unroll
-            for (int q = 0; q < kKP; ++q) V16::unpack(lds128(sbase + q * p.pass_bytes), v[q]);
-            float smax = kNegInf;
+        for (int q = 0; q < kKP; ++q) {
+            const int rho = rr + q * p.R;
+            zo[q] = rho / p.H;
+            yo[q] = rho - zo[q] * p.H;
+        }
+        for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
+            const Item it = decode(p, w);
+            float m = kNegInf, mL = kNegInf;
+            float c[kKP][VEC];
 #pragma unroll
             for (int q = 0; q < kKP; ++q)
 #pragma unroll
-                for (int j = 0; j < VEC; ++j) smax = fmaxf(smax, v[q][j]);
-            if (smax > st.m) {
-                const float f = rebase_w(st.m, smax);
+                for (int j = 0; j < VEC; ++j) c[q][j] = 0.f;
+            double s0t = 0.0, syb = 0.0, szb = 0.0;
+            int rowbase = it.sv0 * p.SR;
+            int zb = rowbase / p.H;
+            int yb = rowbase - zb * p.H;
+            for (int s = 0; s < it.n; ++s, ++g) {
+                const unsigned slot = g % kSlots;
+                mbar_wait_bounded(smem_u32(&sm.full[slot]), (g / kSlots) & 1);
+                if (active) {
+                    const uint32_t sbase = lds_base + slot * kSlotBytes;
+                    float v[kKP][VEC];
 #pragma unroll
-                for (int q = 0; q < kKP; ++q)
+                    for (int q = 0; q < kKP; ++q) V16::unpack(lds128(sbase + q * p.pass_bytes), v[q]);
+                    float smax = kNegInf;
 #pragma unroll
-                    for (int j = 0; j < VEC; ++j) st.c[q][j] *= f;
-                const double fd = (double)f;
-                st.s0t *= fd; st.syb *= fd; st.szb *= fd;
-                st.m = smax;
-                st.mL = __fmul_rn(smax, kLog2e);
+                    for (int q = 0; q < kKP; ++q)
+#pragma unroll
+                        for (int j = 0; j < VEC; ++j) smax = fmaxf(smax, v[q][j]);
+                    if (smax > m) {
+                        const float f = rebase_w(m, smax);
+#pragma unroll
+                        for (int q = 0; q < kKP; ++q)
+#pragma unroll
+                            for (int j = 0; j < VEC; ++j) c[q][j] *= f;
+                        const double fd = (double)f;
+                        s0t *= fd; syb *= fd; szb *= fd;
+                        m = smax;
+                        mL = __fmul_rn(smax, kLog2e);
+                    }
+                    // all -inf so far: exponentiate against 0 so that e = 2^-inf = 0 (no NaN)
+                    const float off = (m == kNegInf) ? 0.f : mL;
+                    float rowsum[kKP];
+#pragma unroll
+                    for (int q = 0; q < kKP; ++q) {
+                        float e[VEC];
+#pragma unroll
+                        for (int j = 0; j < VEC; ++j) {
+                            e[j] = ex2(fmaf(v[q][j], kLog2e, -off));
+                            c[q][j] += e[j];
+                        }
+                        if constexpr (kStash)
+                            sts128(sbase + q * p.pass_bytes, make_uint4(__float_as_uint(e[0]), __float_as_uint(e[1]),
+                                                                        __float_as_uint(e[2]), __float_as_uint(e[3])));
+                        if constexpr (VEC == 4)
+                            rowsum[q] = (e[0] + e[1]) + (e[2] + e[3]);
+                        else
+                            rowsum[q] = ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[VEC - 1]));
+                    }
+                    if constexpr (kStash) sm.mls[slot][tid] = mL;
+                    const double dt = (double)((rowsum[0] + rowsum[1]) + (rowsum[2] + rowsum[3]));
+                    s0t += dt;
+                    syb = fma((double)yb, dt, syb);
+                    szb = fma((double)zb, dt, szb);
+                }
+                // next stage's base row (uniform): SR | H or H | SR, so one of the two moves
+                yb += p.SR;
+                while (yb >= p.H) { yb -= p.H; ++zb; }
             }
-            // all -inf so far: exponentiate against 0 so that e = 2^-inf = 0 (no NaN)
-            const float off = (st.m == kNegInf) ? 0.f : st.mL;
-            float rowsum[kKP];
+            // the item is stashed: hand it to the write team (release of this warp's smem writes)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&sm.red_done[item_no % kRD]));
+            // ---- fold the thread's accumulators, merge over the team, publish the item's partial ----
+            double q7[kNSums];
 #pragma unroll
-            for (int q = 0; q < kKP; ++q) {
-                float e[VEC];
+            for (int k = 0; k < kNSums; ++k) q7[k] = 0.0;
+            float pmx = kNegInf;
+            if (active) {
+                pmx = m;
+                double col[VEC];
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) col[j] = 0.0;
+#pragma unroll
+                for (int q = 0; q < kKP; ++q) {
+                    double row = 0.0;
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) {
+                        const double cd = (double)c[q][j];
+                        row += cd;
+                        col[j] += cd;
+                    }
+                    q7[2] = fma((double)yo[q], row, q7[2]);
+                    q7[3] = fma((double)zo[q], row, q7[3]);
+                }
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) {
-                    e[j] = ex2(fmaf(v[q][j], kLog2e, -off));
-                    st.c[q][j] += e[j];
+                    q7[0] += col[j];
+                    q7[1] = fma((double)(x0 + j), col[j], q7[1]);
                 }
-                if constexpr (kStash) {
-                    static_assert(!kStash || VEC == 4, "stash is in place: fp32 logits only");
-                    sts128(sbase + q * p.pass_bytes, make_uint4(__float_as_uint(e[0]), __float_as_uint(e[1]),
-                                                                __float_as_uint(e[2]), __float_as_uint(e[VEC - 1])));
-                }
-                float r = 0.f;
-                if constexpr (VEC == 4) {
-                    r = (e[0] + e[1]) + (e[2] + e[3]);
-                } else {
-                    r = ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
-                }
-                rowsum[q] = r;
+                q7[4] = s0t; q7[5] = syb; q7[6] = szb;
             }
-            if constexpr (kStash) sm.mls[slot][tid] = st.mL;
-            const float t = (rowsum[0] + rowsum[1]) + (rowsum[2] + rowsum[3]);
-            const int rowbase = (it.sv0 + s) * p.SR;
-            const int zb = rowbase / p.H;
-            const int yb = rowbase - zb * p.H;
-            const double dt = (double)t;
-            st.s0t += dt;
-            st.syb = fma((double)yb, dt, st.syb);
-            st.szb = fma((double)zb, dt, st.szb);
-        }
-    };
-
-    // ---- fold the thread's accumulators, merge over the CTA, publish the item's partial ----
-    auto publish = [&](const Item& it) {
-        double q7[kNSums];
+            const float wm = warp_max(pmx);
+            const double f = (double)rebase_w(pmx, wm);
 #pragma unroll
-        for (int k = 0; k < kNSums; ++k) q7[k] = 0.0;
-        float m = kNegInf;
-        if (active) {
-            m = st.m;
-            double col[VEC];
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) col[j] = 0.0;
-#pragma unroll
-            for (int q = 0; q < kKP; ++q) {
-                double row = 0.0;
-#pragma unroll
-                for (int j = 0; j < VEC; ++j) {
-                    const double cd = (double)st.c[q][j];
-                    row += cd;
-                    col[j] += cd;
-                }
-                const int rho = rr + q * p.R;
-                const int zo = rho / p.H;
-                const int yo = rho - zo * p.H;
-                q7[2] = fma((double)yo, row, q7[2]);
-                q7[3] = fma((double)zo, row, q7[3]);
-            }
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) {
-                q7[0] += col[j];
-                q7[1] = fma((double)(x0 + j), col[j], q7[1]);
-            }
-            q7[4] = st.s0t; q7[5] = st.syb; q7[6] = st.szb;
-        }
-        const float wm = warp_max(m);
-        const double f = (double)rebase_w(m, wm);
-#pragma unroll
-        for (int k = 0; k < kNSums; ++k) q7[k] = warp_sum(q7[k] * f);
-        if (lane == 0) {
-#pragma unroll
-            for (int k = 0; k < kNSums; ++k) sm.wred[warp][k] = q7[k];
-            sm.wmax[warp] = wm;
-        }
-        consumer_barrier();
-        if (warp == 0) {
-            float pm = (lane < kNW) ? sm.wmax[lane] : kNegInf;
-            double a[kNSums];
-#pragma unroll
-            for (int k = 0; k < kNSums; ++k) a[k] = (lane < kNW) ? sm.wred[lane][k] : 0.0;
-            float cm = pm;
-#pragma unroll
-            for (int o = kNW / 2; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
-            const double f2 = (double)rebase_w(pm, cm);
-#pragma unroll
-            for (int k = 0; k < kNSums; ++k) {
-                a[k] *= f2;
-#pragma unroll
-                for (int o = kNW / 2; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
-            }
+            for (int k = 0; k < kNSums; ++k) q7[k] = warp_sum(q7[k] * f);
             if (lane == 0) {
-                double* dst = p.partials + (it.vol * p.P + it.i) * 8;
 #pragma unroll
-                for (int k = 0; k < kNSums; ++k) __stcg(dst + k, a[k]);
-                __stcg(dst + 7, (double)cm);
-                __threadfence();
-                atomicAdd(p.counters + it.vol, 1u);
+                for (int k = 0; k < kNSums; ++k) sm.wred[warp][k] = q7[k];
+                sm.wmax[warp] = wm;
             }
-        }
-    };
-
-    // per-item scalars of the item being written
-    float ML = 0.f;
-    float ax[VEC];
+            team_barrier<1>();
+            if (warp == 0) {
+                const float pm = (lane < kNW) ? sm.wmax[lane] : kNegInf;
+                double a[kNSums];
 #pragma unroll
-    for (int j = 0; j < VEC; ++j) ax[j] = 0.f;
+                for (int k = 0; k < kNSums; ++k) a[k] = (lane < kNW) ? sm.wred[lane][k] : 0.0;
+                float cm = pm;
+#pragma unroll
+                for (int o = kNW / 2; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+                const double f2 = (double)rebase_w(pm, cm);
+#pragma unroll
+                for (int k = 0; k < kNSums; ++k) {
+                    a[k] *= f2;
+#pragma unroll
+                    for (int o = kNW / 2; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
+                }
+                if (lane == 0) {
+                    double* dst = p.partials + (it.vol * p.P + it.i) * 8;
+#pragma unroll
+                    for (int k = 0; k < kNSums; ++k) __stcg(dst + k, a[k]);
+                    __stcg(dst + 7, (double)cm);
+                    __threadfence();
+                    atomicAdd(p.counters + it.vol, 1u);
+                }
+            }
+            team_barrier<1>();   // wred / wmax are free again
+        }
+        return;
+    }
 
-    // ---- wait for all partials of the volume, merge, L1 gradient, per-row terms ----
-    auto wait_and_scalars = [&](const Item& it) {
+    // ================================ WRITE team ================================
+    unsigned g = 0;
+    unsigned item_no = 0;
+    for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
+        const Item it = decode(p, w);
         if (warp == 0) {
+            // targets first: their latency overlaps the flag wait
+            double tk = 0.0, wk = 0.0;
+            if (lane < 3) {
+                tk = p.tgt_f64 ? reinterpret_cast<const double*>(p.gt)[it.vol * 3 + lane]
+                               : (double)reinterpret_cast<const float*>(p.gt)[it.vol * 3 + lane];
+                wk = p.tgt_f64 ? reinterpret_cast<const double*>(p.vis)[it.vol * 3 + lane]
+                               : (double)reinterpret_cast<const float*>(p.vis)[it.vol * 3 + lane];
+            }
             unsigned spins = 0;
             while (ld_acquire_u32(p.counters + it.vol) < (unsigned)p.P) {
-                __nanosleep(64);
+                __nanosleep(20);
                 if (++spins > kSpinLimit) {
                     if (lane == 0) atomicExch(p.err, 1u);
                     break;
@@ -381,77 +394,70 @@ __global__ void __launch_bounds__(kC + 32, 1) k_resident(const Params p) {
                 for (int k = 0; k < 8; ++k) b[k] = __ldcg(src + k);
                 const float pm = (float)b[7];
                 if (pm > mi) {
-                    const double f = (double)rebase_w(mi, pm);
+                    const double fr = (double)rebase_w(mi, pm);
 #pragma unroll
-                    for (int k = 0; k < kNSums; ++k) a[k] *= f;
+                    for (int k = 0; k < kNSums; ++k) a[k] *= fr;
                     mi = pm;
                 }
-                const double f = (double)rebase_w(pm, mi);
+                const double fr = (double)rebase_w(pm, mi);
 #pragma unroll
-                for (int k = 0; k < kNSums; ++k) a[k] = fma(f, b[k], a[k]);
+                for (int k = 0; k < kNSums; ++k) a[k] = fma(fr, b[k], a[k]);
             }
             const float M = warp_max(mi);
-            const double f = (double)rebase_w(mi, M);
+            const double fr = (double)rebase_w(mi, M);
 #pragma unroll
-            for (int k = 0; k < kNSums; ++k) a[k] = warp_sum(a[k] * f);
-            if (lane == 0) {
-                // loss.py:39-41 (expectations) and :54-56 (normalisation), in fp64, rounded once
-                const double ex_ = a[1] / a[0];
-                const double ey_ = a[2] / a[0] + a[5] / a[4];
-                const double ez_ = a[3] / a[0] + a[6] / a[4];
-                const float cxn = (float)(ex_ / (double)p.W - 0.5);
-                const float cyn = (float)(ey_ / (double)p.H - 0.5);
-                const float czn = (float)(ez_ / (double)p.D - 0.5);
-                const double c3[3] = {(double)cxn, (double)cyn, (double)czn};
-                float g3[3];
-                // loss.py:86-89 on this volume's three coordinates, in the targets' precision
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const double tk = p.tgt_f64 ? reinterpret_cast<const double*>(p.gt)[it.vol * 3 + k]
-                                                : (double)reinterpret_cast<const float*>(p.gt)[it.vol * 3 + k];
-                    const double wk = p.tgt_f64 ? reinterpret_cast<const double*>(p.vis)[it.vol * 3 + k]
-                                                : (double)reinterpret_cast<const float*>(p.vis)[it.vol * 3 + k];
-                    const double dlt = c3[k] - tk;
-                    const double sg = (dlt > 0.0) ? 1.0 : ((dlt < 0.0) ? -1.0 : 0.0);
-                    g3[k] = (float)(sg * wk * p.norm);
-                    if (it.i == 0 && p.loss_terms) p.loss_terms[it.vol * 3 + k] = fabs(dlt) * wk;
-                }
+            for (int k = 0; k < kNSums; ++k) a[k] = warp_sum(a[k] * fr);
+            // loss.py:39-41 (expectations) and :54-56 (normalisation), in fp64, rounded once.
+            // Lane k (< 3) finishes axis k: x, y, z.
+            const double ic = 1.0 / a[0], itt = 1.0 / a[4];
+            const double num_c = lane == 0 ? a[1] : (lane == 1 ? a[2] : a[3]);
+            const double num_t = lane == 0 ? 0.0 : (lane == 1 ? a[5] : a[6]);
+            const double dim = lane == 0 ? (double)p.W : (lane == 1 ? (double)p.H : (double)p.D);
+            const double ex_ = num_c * ic + (lane == 0 ? 0.0 : num_t * itt);
+            const float cn = (float)(ex_ / dim - 0.5);
+            // loss.py:86-89 on this volume's three coordinates, in the targets' precision
+            const double dlt = (double)cn - tk;
+            const double sg = (dlt > 0.0) ? 1.0 : ((dlt < 0.0) ? -1.0 : 0.0);
+            const float g1 = (float)(sg * wk * p.norm);
+            if (lane < 3) {
                 if (it.i == 0) {
-                    if (p.coords) { p.coords[it.vol * 3 + 0] = cxn; p.coords[it.vol * 3 + 1] = cyn; p.coords[it.vol * 3 + 2] = czn; }
-                    if (p.expect) { p.expect[it.vol * 3 + 0] = ex_; p.expect[it.vol * 3 + 1] = ey_; p.expect[it.vol * 3 + 2] = ez_; }
-                    if (p.stats) { p.stats[it.vol * 2 + 0] = M; p.stats[it.vol * 2 + 1] = (float)a[0]; }
+                    if (p.loss_terms) p.loss_terms[it.vol * 3 + lane] = fabs(dlt) * wk;
+                    if (p.coords) p.coords[it.vol * 3 + lane] = cn;
+                    if (p.expect) p.expect[it.vol * 3 + lane] = ex_;
                 }
-                sm.finE[0] = ex_; sm.finE[1] = ey_; sm.finE[2] = ez_;
-                sm.finL = a[0];
-                sm.fin[0] = M; sm.fin[1] = g3[0]; sm.fin[2] = g3[1]; sm.fin[3] = g3[2];
+                sm.finE[lane] = ex_;
+                sm.finK[lane] = (double)g1 / dim * ic;     // g_a / dim_a / L
+            }
+            if (lane == 0) {
+                sm.finM = M;
+                if (it.i == 0 && p.stats) { p.stats[it.vol * 2 + 0] = M; p.stats[it.vol * 2 + 1] = (float)a[0]; }
             }
         }
-        consumer_barrier();
-        const double L = sm.finL;
-        const double kxd = (double)sm.fin[1] / (double)p.W / L;
-        const double kyd = (double)sm.fin[2] / (double)p.H / L;
-        const double kzd = (double)sm.fin[3] / (double)p.D / L;
+        team_barrier<2>();
+        const double kxd = sm.finK[0], kyd = sm.finK[1], kzd = sm.finK[2];
         const double Ex = sm.finE[0], Ey = sm.finE[1], Ez = sm.finE[2];
-        ML = __fmul_rn(sm.fin[0], kLog2e);
+        const float ML = __fmul_rn(sm.finM, kLog2e);
+        float ax[VEC];
 #pragma unroll
         for (int j = 0; j < VEC; ++j) ax[j] = (float)(kxd * ((double)(x0 + j) - Ex));
-        // (idx - E) keeps its absolute accuracy: formed in fp64 per row, rounded once
-        const int nrows = it.n * p.SR;
-        const int row0 = it.sv0 * p.SR;
-        for (int lr = tid; lr < nrows; lr += kC) {
-            const int row = row0 + lr;
-            const int z = row / p.H;
-            const int y = row - z * p.H;
-            sm.rt[lr] = (float)(kyd * ((double)y - Ey) + kzd * ((double)z - Ez));
+        {
+            // per-row term: (idx - E) keeps its absolute accuracy, formed in fp64, rounded once
+            const int nrows = it.n * p.SR;
+            const int row0 = it.sv0 * p.SR;
+            for (int lr = tid; lr < nrows; lr += kC) {
+                const int row = row0 + lr;
+                const int z = row / p.H;
+                const int y = row - z * p.H;
+                sm.rt[lr] = (float)(kyd * ((double)y - Ey) + kzd * ((double)z - Ez));
+            }
         }
-        consumer_barrier();
-    };
+        team_barrier<2>();   // rt visible; fin* may be overwritten after the NEXT barrier pair only
+        // the reduce team has stashed every stage of this item
+        mbar_wait_bounded(smem_u32(&sm.red_done[item_no % kRD]), (item_no / kRD) & 1);
 
-    // ---- write the gradient of every stage of `it` from the ring, releasing the slots ----
-    auto write_item = [&](const Item& it) {
         unsigned char* gdst = p.out + it.vol * p.vol_bytes + (long long)it.sv0 * p.stage_bytes + 16ll * tid;
-        for (int s = 0; s < it.n; ++s, ++g_wr) {
-            const unsigned slot = g_wr % kSlots;
+        for (int s = 0; s < it.n; ++s, ++g) {
+            const unsigned slot = g % kSlots;
             if (active) {
                 const uint32_t sbase = lds_base + slot * kSlotBytes;
                 float f = 1.f;
@@ -483,34 +489,6 @@ __global__ void __launch_bounds__(kC + 32, 1) k_resident(const Params p) {
                 mbar_arrive(smem_u32(&sm.empty[slot]));
             }
         }
-    };
-
-    long long w = blockIdx.x;
-    Item nxt;
-    if (w < p.n_items) {
-        nxt = decode(p, w);
-        st.init();
-        reduce_stages(nxt, 0, nxt.n);
-        publish(nxt);
-    }
-    while (w < p.n_items) {
-        const Item cur = nxt;
-        const long long wn = w + gridDim.x;
-        const bool has_next = wn < p.n_items;
-        int head = 0;
-        if (has_next) {
-            nxt = decode(p, wn);
-            st.init();
-            head = min(nxt.n, kSlots - cur.n);
-            reduce_stages(nxt, 0, head);
-        }
-        wait_and_scalars(cur);
-        write_item(cur);
-        if (has_next) {
-            reduce_stages(nxt, head, nxt.n);
-            publish(nxt);
-        }
-        w = wn;
     }
 }
 
@@ -596,7 +574,7 @@ extern "C" int hipe_joint_loss_resident(const void* logits, int dtype, long long
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, res::kC + 32, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 2 * res::kC + 32, smem);
     if (e != cudaSuccess) return (int)e;
     if (occ < 1) return HIPE_E_UNSUPPORTED;
     long long grid = (long long)sms;   // one CTA per SM: the ring takes the whole shared memory
@@ -627,7 +605,7 @@ extern "C" int hipe_joint_loss_resident(const void* logits, int dtype, long long
     e = cudaMemsetAsync(workspace, 0, cb, st);
     if (e != cudaSuccess) return (int)e;
     void* args[] = {(void*)&p};
-    e = cudaLaunchCooperativeKernel(kern, dim3((unsigned)grid), dim3(res::kC + 32), args, smem, st);
+    e = cudaLaunchCooperativeKernel(kern, dim3((unsigned)grid), dim3(2 * res::kC + 32), args, smem, st);
     if (e == cudaErrorCooperativeLaunchTooLarge) {
         (void)cudaGetLastError();
         return HIPE_E_UNSUPPORTED;
