@@ -1,38 +1,38 @@
-// JointLocationLoss forward + backward in ONE persistent launch that reads every heatmap volume
-// from HBM exactly once and writes its gradient exactly once (sm_100a).
+// JointLocationLoss forward + backward in ONE persistent launch in which HBM sees every heatmap
+// volume once on the way in and its gradient once on the way out (sm_100a).
 //
 // Replaces common/nets/loss.py:74-91 followed by loss.backward() (main/train.py:113) of the
 // reference.  The two-launch path (hipe_softargmax_fwd + hipe_softargmax_bwd) moves
-// 2 V s + V g bytes per volume; this launch moves V s + V g: the volume stays ON CHIP between
-// the reduction and the gradient write.
+// 2 V s + V g bytes per volume through HBM; this launch moves V s + V g: the second read of
+// the logits, which the gradient needs, is served ON CHIP by the 126 MB L2, because the
+// gradient pass trails the reduction pass by a bounded window of a few hundred KB per SM.
 //
-// A 64^3 fp32 volume is 1 MiB, more than one SM's shared memory, so a volume is cut into P
-// ITEMS of <= 4 stages (a stage = SR whole rows <= 16 KB) and the items of one volume are
-// taken by P different CTAs of a persistent grid (one CTA per SM, cooperative launch so that
-// all of them are co-resident).  Per CTA:
+// A persistent grid (one CTA per SM, cooperative launch: all CTAs co-resident) walks the batch
+// in ITEMS: a volume is cut into P items of <= 8 stages, a stage is SR whole rows (<= 16 KB),
+// and the P items of one volume go to P different CTAs.  Every CTA runs two decoupled
+// 256-thread teams, each fed by its own TMA producer warp and its own shared-memory ring:
 //
-//   producer warp   streams the CTA's items, stage by stage, into a 13-slot x 16 KB ring with
-//                   1-D TMA bulk copies (evict_first: HBM lines are never needed again);
-//   reduce team     (256 threads) REDUCE a stage: online-max softmax; the exponentials are
-//                   written back over the logits in the ring slot ("stash", fp32 only) together with the offset
-//                   they are relative to, so the gradient pass needs no second MUFU.EX2;
-//                   per-thread fp32 accumulators per owned (row-in-stage, column) position;
-//                   PUBLISH the item's partial sums to a global workspace and bump the
-//                   volume's arrival counter (release);
-//   write team      (256 threads)
-//                   WAIT until the counter shows all P partials (acquire), merge them in a
-//                   fixed order (every CTA of the volume computes bit-identical scalars), form
-//                   the L1 gradient sign(c-gt)*vis*norm (loss.py:86-89);
-//                   WRITE: dlogits = e*2^(off-M)/L * (gx(x-Ex)/W + gy(y-Ey)/H + gz(z-Ez)/D)
-//                   from the stashed ring slot, then release the slot to the producer.
+//   REDUCE team   streams its items (1-D TMA bulk copies, L2 evict_last): online-max softmax,
+//                 per-thread fp32 accumulators per owned (row-in-stage, column) position, folded
+//                 to fp64 per item; PUBLISHES the item's partial sums to a global workspace and
+//                 bumps the volume's arrival counter (release).  Never waits on another CTA.
+//   WRITE team    for the same items, up to `lag` items behind: WAITS until the volume's counter
+//                 shows all P partials (acquire), merges them in a fixed order (every CTA of the
+//                 volume computes bit-identical scalars), forms the L1 gradient
+//                 sign(c-gt)*vis*norm (loss.py:86-89), streams the item AGAIN (TMA, L2 hit,
+//                 evict_first) and writes
+//                 dlogits = e/L * (gx(x-Ex)/W + gy(y-Ey)/H + gz(z-Ez)/D).
 //
-// REDUCE/PUBLISH and WAIT/WRITE are done by two different 256-thread teams of the CTA working
-// on consecutive items through the same ring: the reduce team runs up to (13 - n) stages (2-3 items) ahead
-// of the write team, so the cross-CTA latency (global flag round trip, ~1 us) and each team's
-// per-item serial work are covered by the other team's streaming and the ring always has loads
-// in flight.  A reduce team never waits on another CTA, a write team only waits on volumes
-// whose items were all published by reduce teams that needed strictly earlier volumes to
-// drain: with all CTAs co-resident (cooperative launch) the schedule cannot deadlock.
+// The reduce producer is throttled to stay at most `lag` items ahead of the write team, which
+// bounds the L2 window to grid * lag * 128 KB (57 MB at lag 3) and gives the write team enough
+// slack that the skew between the CTAs sharing a volume never stalls it.  A first version kept
+// the exponentials in a 13-slot shared-memory ring instead of re-reading through L2; with so
+// little look-ahead every item behaved like a barrier across the P CTAs (write team polling the
+// flag ~17 times per item, 0.59 ms per 1344 volumes of 64^3 fp32 against 0.43 ms at HBM speed).
+//
+// Deadlock freedom: reduce teams depend only on their own write team's progress on EARLIER
+// items; write teams wait on volumes whose partials come from reduce teams: no cycle, provided
+// all CTAs are co-resident.
 //
 // Precision (same contract as hipe_stream_kernel.cuh): exponentials are fp32; each expectation
 // is a ratio of fp64 sums built from the SAME rounded fp32 atoms, so rounding only re-weights
@@ -47,16 +47,23 @@
 namespace hipe {
 namespace res {
 
-constexpr int kC = 256;               // consumer threads
-constexpr int kNW = kC / 32;          // consumer warps
-constexpr int kSlots = 13;            // ring depth
+constexpr int kC = 256;               // threads per team
+constexpr int kNW = kC / 32;          // warps per team
+constexpr int kRSlots = 7;            // reduce ring depth (HBM latency to cover)
+constexpr int kWSlots = 6;            // write ring depth (L2 latency to cover)
 constexpr int kSlotBytes = 16384;     // ring slot
 constexpr int kKP = 4;                // 16-byte vectors per thread per stage
-constexpr int kMaxItemStages = 4;     // an item never exceeds 4 stages (64 KB): >= 2 whole items of look-ahead in the ring
-constexpr int kRD = 16;               // reduce->write hand-off barriers (the ring never holds more than 13 items)
-constexpr int kMaxRtRows = 1024;      // rows of one item (<= 4 stages x 256 rows)
+constexpr int kMaxItemStages = 16;    // unroll bound: an item never exceeds 16 stages (256 KB)
+constexpr int kDefItemStages = 8;     // default item size in stages (128 KB)
+constexpr int kMaxRtRows = 1024;      // rows of one item (<= 8 stages x 128 rows)
 constexpr int kNSums = 7;             // S0c Sx Syo Szo S0t Syb Szb
+constexpr int kRD = 32;               // write-team progress barriers (> any lag)
+constexpr int kMaxLag = 24;
+constexpr int kNB = 8;                // scalar records in flight (scalar warp -> write team)
+constexpr int kPB = 4;                // per-item warp partials in flight (reduce team -> publish warp)
+constexpr int kThreads = 2 * kC + 128; // two teams + two producer warps + the scalar warp + the publish warp
 constexpr unsigned kSpinLimit = 1u << 22;
+constexpr float kLazy = 16.f;         // lazy re-basing threshold of the online softmax (natural-log units)
 
 struct Params {
     const unsigned char* in;
@@ -66,13 +73,14 @@ struct Params {
     long long n_items;
     int W, H, D;
     int G;            // 16-byte column groups per row
-    int R;            // rows per visit of the CTA
+    int R;            // rows per visit of a team
     int SR;           // rows per stage (= kKP * R); SR | H or H | SR
     int stage_bytes;  // SR * row bytes (<= 16 KB)
     int pass_bytes;   // R * row bytes
-    int nact;         // active consumer threads (= R * G)
+    int nact;         // active threads per team (= R * G)
     int NSv;          // stages per volume
     int P;            // items per volume
+    int lag;          // items the reduce side may run ahead of the write side
     // outputs (nullable except out)
     float* coords;
     double* expect;
@@ -90,16 +98,21 @@ struct Params {
 };
 
 struct Smem {
-    float mls[kSlots][kC];        // offset (in log2 units) the stashed exponentials of (slot, thread) are relative to
-    float rt[kMaxRtRows];         // per-row gradient term of the item being written
-    unsigned long long full[kSlots];
-    unsigned long long empty[kSlots];
-    unsigned long long red_done[kRD];  // reduce team -> write team: every stage of the item is stashed
-    double wred[kNW][8];          // reduce team scratch
-    float wmax[kNW];
-    double finE[3];               // write team: Ex, Ey, Ez
-    double finK[3];               //             g_a / dim_a / L per axis
-    float finM;                   //             volume maximum
+    float rt[2][kMaxRtRows];      // per-row gradient term of the item being written (double-buffered)
+    unsigned long long rfull[kRSlots], rempty[kRSlots];
+    unsigned long long wfull[kWSlots], wempty[kWSlots];
+    unsigned long long w_done[kRD];   // write team finished item (index item_no % kRD)
+    unsigned long long scal_ready[kNB];   // scalar warp -> write team
+    unsigned long long red_ready[kPB];    // reduce team (kNW arrivals) -> publish warp
+    unsigned long long red_free[kPB];     // publish warp -> reduce team
+    double wred[kPB][kNW][8];     // per-warp partials of an item
+    float wmax[kPB][kNW];
+    struct Scal {
+        double E[3];              // Ex, Ey, Ez
+        double K[3];              // g_a / dim_a / L per axis
+        float M;                  // volume maximum
+        float pad;
+    } scal[kNB];
 };
 
 struct Item {
@@ -141,11 +154,6 @@ __device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity)
     __trap();
 }
 
-__device__ __forceinline__ void sts128(uint32_t saddr, const uint4& v) {
-    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
-                 : "memory");
-}
-
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
     unsigned v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -157,216 +165,99 @@ __device__ __forceinline__ float rebase_w(float m_from, float m_to) {
     return (m_from == kNegInf) ? 0.f : ex2(__fsub_rn(__fmul_rn(m_from, kLog2e), __fmul_rn(m_to, kLog2e)));
 }
 
-// Thread roles inside the CTA (kThreads = 2*kC + 32):
-//   [0, kC)        REDUCE team: online softmax + stash + publish of item k+1
-//   [kC, 2kC)      WRITE team : flag wait + scalars + gradient write of item k, releases slots
-//   [2kC, 2kC+32)  producer warp (one elected lane)
-// The reduce team runs at most 13 - n stages ahead of the write team (ring capacity), which is
-// what hides the cross-CTA flag latency and the per-item serial work of either team.
-template <typename T, bool kStash>
-__global__ void __launch_bounds__(2 * kC + 32, 1) k_resident(const Params p) {
+// Thread roles inside the CTA (kThreads = 2*kC + 64):
+//   [0, kC)          REDUCE team
+//   [kC, 2kC)        WRITE team
+//   warp 2kC/32      reduce-ring producer (one elected lane), throttled by the write team
+//   warp 2kC/32 + 1  write-ring producer (one elected lane)
+//   warp 2kC/32 + 2  scalar warp: flag wait, merge of the P partials, L1 gradient
+//   warp 2kC/32 + 3  publish warp: merges the reduce team's warp partials, writes + flags them
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
     using V16 = Vec16<T>;
     constexpr int VEC = V16::N;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kSlots * kSlotBytes);
-    const uint32_t ring = smem_u32(smem_raw);
+    Smem& sm = *reinterpret_cast<Smem*>(smem_raw + (kRSlots + kWSlots) * kSlotBytes);
+    const uint32_t rring = smem_u32(smem_raw);
+    const uint32_t wring = rring + kRSlots * kSlotBytes;
 
     if (threadIdx.x == 0) {
 #pragma unroll
-        for (int s = 0; s < kSlots; ++s) {
-            mbar_init(smem_u32(&sm.full[s]), 1);
-            mbar_init(smem_u32(&sm.empty[s]), kNW);
+        for (int s = 0; s < kRSlots; ++s) {
+            mbar_init(smem_u32(&sm.rfull[s]), 1);
+            mbar_init(smem_u32(&sm.rempty[s]), kNW);
         }
 #pragma unroll
-        for (int s = 0; s < kRD; ++s) mbar_init(smem_u32(&sm.red_done[s]), kNW);
+        for (int s = 0; s < kWSlots; ++s) {
+            mbar_init(smem_u32(&sm.wfull[s]), 1);
+            mbar_init(smem_u32(&sm.wempty[s]), kNW);
+        }
+#pragma unroll
+        for (int s = 0; s < kRD; ++s) mbar_init(smem_u32(&sm.w_done[s]), kNW);
+#pragma unroll
+        for (int s = 0; s < kNB; ++s) mbar_init(smem_u32(&sm.scal_ready[s]), 1);
+#pragma unroll
+        for (int s = 0; s < kPB; ++s) {
+            mbar_init(smem_u32(&sm.red_ready[s]), kNW);
+            mbar_init(smem_u32(&sm.red_free[s]), 1);
+        }
         mbar_fence_init();
         fence_proxy_async();
     }
     __syncthreads();
 
-    if (threadIdx.x >= 2 * kC) {
-        // ------------------------------ producer warp ------------------------------
-        if (threadIdx.x == 2 * kC) {
-            const uint64_t pol = policy_evict_first();
-            unsigned g = 0;
-            for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x) {
-                const Item it = decode(p, w);
-                const unsigned char* src = p.in + it.vol * p.vol_bytes + (long long)it.sv0 * p.stage_bytes;
-                for (int s = 0; s < it.n; ++s, ++g) {
-                    const unsigned slot = g % kSlots;
-                    if (g >= (unsigned)kSlots) mbar_wait_bounded(smem_u32(&sm.empty[slot]), ((g / kSlots) - 1) & 1);
-                    const uint32_t bar = smem_u32(&sm.full[slot]);
-                    mbar_arrive_expect_tx(bar, (uint32_t)p.stage_bytes);
-                    tma_load_1d(ring + slot * kSlotBytes, src + (long long)s * p.stage_bytes, (uint32_t)p.stage_bytes,
-                                bar, pol);
-                }
-            }
-        }
-        return;
-    }
-
-    const bool is_writer = threadIdx.x >= kC;
-    const int tid = is_writer ? threadIdx.x - kC : threadIdx.x;   // team-local
-    const int lane = tid & 31, warp = tid >> 5;
-    const bool active = tid < p.nact;
-    const int cg = active ? tid % p.G : 0;
-    const int rr = active ? tid / p.G : 0;
-    const int x0 = cg * VEC;
-    const uint32_t lds_base = ring + 16u * tid;
-
-    if (!is_writer) {
-        // =============================== REDUCE team ===============================
-        unsigned g = 0, item_no = 0;
-        // row offsets of this thread's kKP visits inside a stage
-        int yo[kKP], zo[kKP];
-#pragma unroll
-        for (int q = 0; q < kKP; ++q) {
-            const int rho = rr + q * p.R;
-            zo[q] = rho / p.H;
-            yo[q] = rho - zo[q] * p.H;
-        }
+    if (threadIdx.x >= 2 * kC + 96) {
+        // ------------------------------- publish warp -------------------------------
+        // Merges the reduce team's kNW warp partials of an item, writes the item's partial to the
+        // workspace and bumps the volume's arrival counter (release).
+        const int lane = threadIdx.x & 31;
+        unsigned item_no = 0;
         for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
             const Item it = decode(p, w);
-            float m = kNegInf, mL = kNegInf;
-            float c[kKP][VEC];
+            const unsigned sb = item_no % kPB;
+            mbar_wait_bounded(smem_u32(&sm.red_ready[sb]), (item_no / kPB) & 1);
+            const float pm = (lane < kNW) ? sm.wmax[sb][lane] : kNegInf;
+            double a[kNSums];
 #pragma unroll
-            for (int q = 0; q < kKP; ++q)
-#pragma unroll
-                for (int j = 0; j < VEC; ++j) c[q][j] = 0.f;
-            double s0t = 0.0, syb = 0.0, szb = 0.0;
-            int rowbase = it.sv0 * p.SR;
-            int zb = rowbase / p.H;
-            int yb = rowbase - zb * p.H;
-            for (int s = 0; s < it.n; ++s, ++g) {
-                const unsigned slot = g % kSlots;
-                mbar_wait_bounded(smem_u32(&sm.full[slot]), (g / kSlots) & 1);
-                if (active) {
-                    const uint32_t sbase = lds_base + slot * kSlotBytes;
-                    float v[kKP][VEC];
-#pragma unroll
-                    for (int q = 0; q < kKP; ++q) V16::unpack(lds128(sbase + q * p.pass_bytes), v[q]);
-                    float smax = kNegInf;
-#pragma unroll
-                    for (int q = 0; q < kKP; ++q)
-#pragma unroll
-                        for (int j = 0; j < VEC; ++j) smax = fmaxf(smax, v[q][j]);
-                    if (smax > m) {
-                        const float f = rebase_w(m, smax);
-#pragma unroll
-                        for (int q = 0; q < kKP; ++q)
-#pragma unroll
-                            for (int j = 0; j < VEC; ++j) c[q][j] *= f;
-                        const double fd = (double)f;
-                        s0t *= fd; syb *= fd; szb *= fd;
-                        m = smax;
-                        mL = __fmul_rn(smax, kLog2e);
-                    }
-                    // all -inf so far: exponentiate against 0 so that e = 2^-inf = 0 (no NaN)
-                    const float off = (m == kNegInf) ? 0.f : mL;
-                    float rowsum[kKP];
-#pragma unroll
-                    for (int q = 0; q < kKP; ++q) {
-                        float e[VEC];
-#pragma unroll
-                        for (int j = 0; j < VEC; ++j) {
-                            e[j] = ex2(fmaf(v[q][j], kLog2e, -off));
-                            c[q][j] += e[j];
-                        }
-                        if constexpr (kStash)
-                            sts128(sbase + q * p.pass_bytes, make_uint4(__float_as_uint(e[0]), __float_as_uint(e[1]),
-                                                                        __float_as_uint(e[2]), __float_as_uint(e[3])));
-                        if constexpr (VEC == 4)
-                            rowsum[q] = (e[0] + e[1]) + (e[2] + e[3]);
-                        else
-                            rowsum[q] = ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[VEC - 1]));
-                    }
-                    if constexpr (kStash) sm.mls[slot][tid] = mL;
-                    const double dt = (double)((rowsum[0] + rowsum[1]) + (rowsum[2] + rowsum[3]));
-                    s0t += dt;
-                    syb = fma((double)yb, dt, syb);
-                    szb = fma((double)zb, dt, szb);
-                }
-                // next stage's base row (uniform): SR | H or H | SR, so one of the two moves
-                yb += p.SR;
-                while (yb >= p.H) { yb -= p.H; ++zb; }
-            }
-            // the item is stashed: hand it to the write team (release of this warp's smem writes)
+            for (int k = 0; k < kNSums; ++k) a[k] = (lane < kNW) ? sm.wred[sb][lane][k] : 0.0;
             __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&sm.red_done[item_no % kRD]));
-            // ---- fold the thread's accumulators, merge over the team, publish the item's partial ----
-            double q7[kNSums];
+            if (lane == 0) mbar_arrive(smem_u32(&sm.red_free[sb]));
+            float cm = pm;
 #pragma unroll
-            for (int k = 0; k < kNSums; ++k) q7[k] = 0.0;
-            float pmx = kNegInf;
-            if (active) {
-                pmx = m;
-                double col[VEC];
+            for (int o = kNW / 2; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+            const double f2 = (double)rebase_w(pm, cm);
 #pragma unroll
-                for (int j = 0; j < VEC; ++j) col[j] = 0.0;
+            for (int k = 0; k < kNSums; ++k) {
+                a[k] *= f2;
 #pragma unroll
-                for (int q = 0; q < kKP; ++q) {
-                    double row = 0.0;
-#pragma unroll
-                    for (int j = 0; j < VEC; ++j) {
-                        const double cd = (double)c[q][j];
-                        row += cd;
-                        col[j] += cd;
-                    }
-                    q7[2] = fma((double)yo[q], row, q7[2]);
-                    q7[3] = fma((double)zo[q], row, q7[3]);
-                }
-#pragma unroll
-                for (int j = 0; j < VEC; ++j) {
-                    q7[0] += col[j];
-                    q7[1] = fma((double)(x0 + j), col[j], q7[1]);
-                }
-                q7[4] = s0t; q7[5] = syb; q7[6] = szb;
+                for (int o = kNW / 2; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
             }
-            const float wm = warp_max(pmx);
-            const double f = (double)rebase_w(pmx, wm);
-#pragma unroll
-            for (int k = 0; k < kNSums; ++k) q7[k] = warp_sum(q7[k] * f);
             if (lane == 0) {
+                double* dst = p.partials + (it.vol * p.P + it.i) * 8;
 #pragma unroll
-                for (int k = 0; k < kNSums; ++k) sm.wred[warp][k] = q7[k];
-                sm.wmax[warp] = wm;
+                for (int k = 0; k < kNSums; ++k) __stcg(dst + k, a[k]);
+                __stcg(dst + 7, (double)cm);
+                __threadfence();
+                atomicAdd(p.counters + it.vol, 1u);
             }
-            team_barrier<1>();
-            if (warp == 0) {
-                const float pm = (lane < kNW) ? sm.wmax[lane] : kNegInf;
-                double a[kNSums];
-#pragma unroll
-                for (int k = 0; k < kNSums; ++k) a[k] = (lane < kNW) ? sm.wred[lane][k] : 0.0;
-                float cm = pm;
-#pragma unroll
-                for (int o = kNW / 2; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
-                const double f2 = (double)rebase_w(pm, cm);
-#pragma unroll
-                for (int k = 0; k < kNSums; ++k) {
-                    a[k] *= f2;
-#pragma unroll
-                    for (int o = kNW / 2; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
-                }
-                if (lane == 0) {
-                    double* dst = p.partials + (it.vol * p.P + it.i) * 8;
-#pragma unroll
-                    for (int k = 0; k < kNSums; ++k) __stcg(dst + k, a[k]);
-                    __stcg(dst + 7, (double)cm);
-                    __threadfence();
-                    atomicAdd(p.counters + it.vol, 1u);
-                }
-            }
-            team_barrier<1>();   // wred / wmax are free again
         }
         return;
     }
 
-    // ================================ WRITE team ================================
-    unsigned g = 0;
-    unsigned item_no = 0;
-    for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
-        const Item it = decode(p, w);
-        if (warp == 0) {
+    if (threadIdx.x >= 2 * kC + 64) {
+        // ------------------------------- scalar warp -------------------------------
+        // Per item: wait for the volume's P partials, merge them, finish the coordinates and the
+        // L1 gradient, and leave the record the write team needs.  Runs ahead of the write team
+        // by up to kNB items, so none of these global round trips is on a team's critical path.
+        const int lane = threadIdx.x & 31;
+        unsigned item_no = 0;
+        for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
+            const Item it = decode(p, w);
+            if (item_no >= (unsigned)kNB) {
+                const unsigned d = item_no - (unsigned)kNB;   // its record slot must have been consumed
+                mbar_wait_bounded(smem_u32(&sm.w_done[d % kRD]), (d / kRD) & 1);
+            }
+            Smem::Scal& rec = sm.scal[item_no % kNB];
             // targets first: their latency overlaps the flag wait
             double tk = 0.0, wk = 0.0;
             if (lane < 3) {
@@ -377,7 +268,7 @@ __global__ void __launch_bounds__(2 * kC + 32, 1) k_resident(const Params p) {
             }
             unsigned spins = 0;
             while (ld_acquire_u32(p.counters + it.vol) < (unsigned)p.P) {
-                __nanosleep(20);
+                __nanosleep(64);
                 if (++spins > kSpinLimit) {
                     if (lane == 0) atomicExch(p.err, 1u);
                     break;
@@ -385,27 +276,27 @@ __global__ void __launch_bounds__(2 * kC + 32, 1) k_resident(const Params p) {
             }
             float mi = kNegInf;
             double a[kNSums];
-#pragma unroll
+    #pragma unroll
             for (int k = 0; k < kNSums; ++k) a[k] = 0.0;
             for (int i = lane; i < p.P; i += 32) {
                 const double* src = p.partials + (it.vol * p.P + i) * 8;
                 double b[8];
-#pragma unroll
+    #pragma unroll
                 for (int k = 0; k < 8; ++k) b[k] = __ldcg(src + k);
                 const float pm = (float)b[7];
                 if (pm > mi) {
                     const double fr = (double)rebase_w(mi, pm);
-#pragma unroll
+    #pragma unroll
                     for (int k = 0; k < kNSums; ++k) a[k] *= fr;
                     mi = pm;
                 }
                 const double fr = (double)rebase_w(pm, mi);
-#pragma unroll
+    #pragma unroll
                 for (int k = 0; k < kNSums; ++k) a[k] = fma(fr, b[k], a[k]);
             }
             const float M = warp_max(mi);
             const double fr = (double)rebase_w(mi, M);
-#pragma unroll
+    #pragma unroll
             for (int k = 0; k < kNSums; ++k) a[k] = warp_sum(a[k] * fr);
             // loss.py:39-41 (expectations) and :54-56 (normalisation), in fp64, rounded once.
             // Lane k (< 3) finishes axis k: x, y, z.
@@ -425,18 +316,218 @@ __global__ void __launch_bounds__(2 * kC + 32, 1) k_resident(const Params p) {
                     if (p.coords) p.coords[it.vol * 3 + lane] = cn;
                     if (p.expect) p.expect[it.vol * 3 + lane] = ex_;
                 }
-                sm.finE[lane] = ex_;
-                sm.finK[lane] = (double)g1 / dim * ic;     // g_a / dim_a / L
+                rec.E[lane] = ex_;
+                rec.K[lane] = (double)g1 / dim * ic;     // g_a / dim_a / L
             }
             if (lane == 0) {
-                sm.finM = M;
+                rec.M = M;
                 if (it.i == 0 && p.stats) { p.stats[it.vol * 2 + 0] = M; p.stats[it.vol * 2 + 1] = (float)a[0]; }
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&sm.scal_ready[item_no % kNB]));
         }
-        team_barrier<2>();
-        const double kxd = sm.finK[0], kyd = sm.finK[1], kzd = sm.finK[2];
-        const double Ex = sm.finE[0], Ey = sm.finE[1], Ez = sm.finE[2];
-        const float ML = __fmul_rn(sm.finM, kLog2e);
+        return;
+    }
+
+    if (threadIdx.x >= 2 * kC) {
+        // ------------------------------ producer warps ------------------------------
+        const bool for_write = threadIdx.x >= 2 * kC + 32;
+        if ((threadIdx.x & 31) == 0) {
+            const uint64_t pol = for_write ? policy_evict_first() : policy_evict_last();
+            const int nslots = for_write ? kWSlots : kRSlots;
+            const uint32_t ring = for_write ? wring : rring;
+            unsigned long long* full = for_write ? sm.wfull : sm.rfull;
+            unsigned long long* empty = for_write ? sm.wempty : sm.rempty;
+            unsigned g = 0, item_no = 0;
+            for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
+                const Item it = decode(p, w);
+                // L2 window: the reduce side stays at most `lag` items ahead of the write side
+                if (!for_write && item_no >= (unsigned)p.lag) {
+                    const unsigned d = item_no - (unsigned)p.lag;
+                    mbar_wait_bounded(smem_u32(&sm.w_done[d % kRD]), (d / kRD) & 1);
+                }
+                const unsigned char* src = p.in + it.vol * p.vol_bytes + (long long)it.sv0 * p.stage_bytes;
+                for (int s = 0; s < it.n; ++s, ++g) {
+                    const unsigned slot = g % nslots;
+                    if (g >= (unsigned)nslots) mbar_wait_bounded(smem_u32(&empty[slot]), ((g / nslots) - 1) & 1);
+                    const uint32_t bar = smem_u32(&full[slot]);
+                    mbar_arrive_expect_tx(bar, (uint32_t)p.stage_bytes);
+                    tma_load_1d(ring + slot * kSlotBytes, src + (long long)s * p.stage_bytes, (uint32_t)p.stage_bytes,
+                                bar, pol);
+                }
+            }
+        }
+        return;
+    }
+
+    const bool is_writer = threadIdx.x >= kC;
+    const int tid = is_writer ? threadIdx.x - kC : threadIdx.x;   // team-local
+    const int lane = tid & 31, warp = tid >> 5;
+    const bool active = tid < p.nact;
+    const int cg = active ? tid % p.G : 0;
+    const int rr = active ? tid / p.G : 0;
+    const int x0 = cg * VEC;
+
+    if (!is_writer) {
+        // =============================== REDUCE team ===============================
+        const uint32_t lds_base = rring + 16u * tid;
+        unsigned g = 0, item_no = 0;
+        // row offsets of this thread's kKP visits inside a stage
+        int yo[kKP], zo[kKP];
+#pragma unroll
+        for (int q = 0; q < kKP; ++q) {
+            const int rho = rr + q * p.R;
+            zo[q] = rho / p.H;
+            yo[q] = rho - zo[q] * p.H;
+        }
+        for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
+            const Item it = decode(p, w);
+            const unsigned sb = item_no % kPB;
+            float m = kNegInf, mL = kNegInf, tm = kNegInf;   // offset in use, fl(m*log2e), true maximum
+            float2 c2[kKP][VEC / 2];
+#pragma unroll
+            for (int q = 0; q < kKP; ++q)
+#pragma unroll
+                for (int j = 0; j < VEC / 2; ++j) c2[q][j] = make_float2(0.f, 0.f);
+            double s0t = 0.0, syb = 0.0, szb = 0.0;
+            int rowbase = it.sv0 * p.SR;
+            int zb = rowbase / p.H;
+            int yb = rowbase - zb * p.H;
+            // Stage s+1 is fetched into registers (and its slot handed back) before the arithmetic
+            // of stage s: two stages' dependency chains overlap in every warp.
+            uint4 raw[2][kKP];
+            auto fetch = [&](unsigned gg, uint4 (&dst)[kKP]) {
+                const unsigned slot = gg % kRSlots;
+                mbar_wait_bounded(smem_u32(&sm.rfull[slot]), (gg / kRSlots) & 1);
+                if (active) {
+                    const uint32_t sbase = lds_base + slot * kSlotBytes;
+#pragma unroll
+                    for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * p.pass_bytes);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&sm.rempty[slot]));
+            };
+            fetch(g, raw[0]);
+#pragma unroll
+            for (int s = 0; s < kMaxItemStages; ++s) {
+                if (s >= it.n) break;
+                if (s + 1 < it.n) fetch(g + s + 1, raw[(s + 1) & 1]);
+                if (active) {
+                    float v[kKP][VEC];
+#pragma unroll
+                    for (int q = 0; q < kKP; ++q) V16::unpack(raw[s & 1][q], v[q]);
+                    float smax = kNegInf;
+#pragma unroll
+                    for (int q = 0; q < kKP; ++q)
+#pragma unroll
+                        for (int j = 0; j < VEC; ++j) smax = fmaxf(smax, v[q][j]);
+                    tm = fmaxf(tm, smax);
+                    // LAZY re-basing: the offset m only moves when a value exceeds it by more than
+                    // kLazy (e <= exp(kLazy) ~ 9e6 stays far inside fp32); the fold re-bases once,
+                    // onto the thread's true maximum tm.  Saves ~30 instructions per stage.
+                    if (smax > m + kLazy) {
+                        const float f = rebase_w(m, smax);
+                        const float2 f2 = make_float2(f, f);
+#pragma unroll
+                        for (int q = 0; q < kKP; ++q)
+#pragma unroll
+                            for (int j = 0; j < VEC / 2; ++j) c2[q][j] = __fmul2_rn(c2[q][j], f2);
+                        const double fd = (double)f;
+                        s0t *= fd; syb *= fd; szb *= fd;
+                        m = smax;
+                        mL = __fmul_rn(smax, kLog2e);
+                    }
+                    // all -inf so far: exponentiate against 0 so that e = 2^-inf = 0 (no NaN)
+                    const float noff = (m == kNegInf) ? 0.f : -mL;
+                    const float2 noff2 = make_float2(noff, noff), l2e2 = make_float2(kLog2e, kLog2e);
+                    float rowsum[kKP];
+#pragma unroll
+                    for (int q = 0; q < kKP; ++q) {
+                        float2 e2[VEC / 2];
+#pragma unroll
+                        for (int j = 0; j < VEC / 2; ++j) {
+                            const float2 a2 = __ffma2_rn(make_float2(v[q][2 * j], v[q][2 * j + 1]), l2e2, noff2);
+                            e2[j] = make_float2(ex2(a2.x), ex2(a2.y));
+                            c2[q][j] = __fadd2_rn(c2[q][j], e2[j]);
+                        }
+                        float2 r2 = __fadd2_rn(e2[0], e2[1]);
+                        if constexpr (VEC == 8) r2 = __fadd2_rn(r2, __fadd2_rn(e2[2], e2[VEC / 2 - 1]));
+                        rowsum[q] = r2.x + r2.y;
+                    }
+                    const float2 t2 = __fadd2_rn(make_float2(rowsum[0], rowsum[2]), make_float2(rowsum[1], rowsum[3]));
+                    const double dt = (double)(t2.x + t2.y);
+                    s0t += dt;
+                    syb = fma((double)yb, dt, syb);
+                    szb = fma((double)zb, dt, szb);
+                }
+                // next stage's base row (uniform): SR | H or H | SR, so one of the two moves
+                yb += p.SR;
+                while (yb >= p.H) { yb -= p.H; ++zb; }
+            }
+            g += it.n;
+            // ---- fold the thread's accumulators, merge over the team, publish the item's partial ----
+            double q7[kNSums];
+#pragma unroll
+            for (int k = 0; k < kNSums; ++k) q7[k] = 0.0;
+            float pmx = kNegInf;
+            if (active) {
+                pmx = tm;
+                double col[VEC];
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) col[j] = 0.0;
+#pragma unroll
+                for (int q = 0; q < kKP; ++q) {
+                    double row = 0.0;
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) {
+                        const double cd = (double)((j & 1) ? c2[q][j / 2].y : c2[q][j / 2].x);
+                        row += cd;
+                        col[j] += cd;
+                    }
+                    q7[2] = fma((double)yo[q], row, q7[2]);
+                    q7[3] = fma((double)zo[q], row, q7[3]);
+                }
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    q7[0] += col[j];
+                    q7[1] = fma((double)(x0 + j), col[j], q7[1]);
+                }
+                q7[4] = s0t; q7[5] = syb; q7[6] = szb;
+                // from the lazy offset onto the thread's true maximum (weight <= 1)
+                const double fl_ = (double)rebase_w(m, tm);
+#pragma unroll
+                for (int k = 0; k < kNSums; ++k) q7[k] *= fl_;
+            }
+            const float wm = warp_max(pmx);
+            const double f = (double)rebase_w(pmx, wm);
+#pragma unroll
+            for (int k = 0; k < kNSums; ++k) q7[k] = warp_sum(q7[k] * f);
+            // hand the warp's partial to the publish warp: no team barrier, nobody waits for the
+            // global round trip
+            if (item_no >= (unsigned)kPB) mbar_wait_bounded(smem_u32(&sm.red_free[sb]), ((item_no / kPB) - 1) & 1);
+            if (lane == 0) {
+#pragma unroll
+                for (int k = 0; k < kNSums; ++k) sm.wred[sb][warp][k] = q7[k];
+                sm.wmax[sb][warp] = wm;
+                mbar_arrive(smem_u32(&sm.red_ready[sb]));
+            }
+        }
+        return;
+    }
+
+    // ================================ WRITE team ================================
+    const uint32_t lds_base = wring + 16u * tid;
+    unsigned g = 0;
+    unsigned item_no = 0;
+    for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
+        const Item it = decode(p, w);
+        mbar_wait_bounded(smem_u32(&sm.scal_ready[item_no % kNB]), (item_no / kNB) & 1);
+        const Smem::Scal& rec = sm.scal[item_no % kNB];
+        float* rt = sm.rt[item_no & 1];
+        const double kxd = rec.K[0], kyd = rec.K[1], kzd = rec.K[2];
+        const double Ex = rec.E[0], Ey = rec.E[1], Ez = rec.E[2];
+        const float ML = __fmul_rn(rec.M, kLog2e);
+        const float2 nML2 = make_float2(-ML, -ML), l2e2 = make_float2(kLog2e, kLog2e);
         float ax[VEC];
 #pragma unroll
         for (int j = 0; j < VEC; ++j) ax[j] = (float)(kxd * ((double)(x0 + j) - Ex));
@@ -448,47 +539,52 @@ __global__ void __launch_bounds__(2 * kC + 32, 1) k_resident(const Params p) {
                 const int row = row0 + lr;
                 const int z = row / p.H;
                 const int y = row - z * p.H;
-                sm.rt[lr] = (float)(kyd * ((double)y - Ey) + kzd * ((double)z - Ez));
+                rt[lr] = (float)(kyd * ((double)y - Ey) + kzd * ((double)z - Ez));
             }
         }
-        team_barrier<2>();   // rt visible; fin* may be overwritten after the NEXT barrier pair only
-        // the reduce team has stashed every stage of this item
-        mbar_wait_bounded(smem_u32(&sm.red_done[item_no % kRD]), (item_no / kRD) & 1);
+        team_barrier<2>();   // rt[b] visible; rt[1-b] is refilled only after every warp has passed here
 
         unsigned char* gdst = p.out + it.vol * p.vol_bytes + (long long)it.sv0 * p.stage_bytes + 16ll * tid;
-        for (int s = 0; s < it.n; ++s, ++g) {
-            const unsigned slot = g % kSlots;
+        uint4 raw[2][kKP];
+        auto fetch = [&](unsigned gg, uint4 (&dst)[kKP]) {
+            const unsigned slot = gg % kWSlots;
+            mbar_wait_bounded(smem_u32(&sm.wfull[slot]), (gg / kWSlots) & 1);
             if (active) {
                 const uint32_t sbase = lds_base + slot * kSlotBytes;
-                float f = 1.f;
-                if constexpr (kStash) f = ex2(__fsub_rn(sm.mls[slot][tid], ML));
-                float fax[VEC];
 #pragma unroll
-                for (int j = 0; j < VEC; ++j) fax[j] = f * ax[j];
-                uint4 raw[kKP];
+                for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * p.pass_bytes);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&sm.wempty[slot]));
+        };
+        fetch(g, raw[0]);
 #pragma unroll
-                for (int q = 0; q < kKP; ++q) raw[q] = lds128(sbase + q * p.pass_bytes);
+        for (int s = 0; s < kMaxItemStages; ++s) {
+            if (s >= it.n) break;
+            if (s + 1 < it.n) fetch(g + s + 1, raw[(s + 1) & 1]);
+            if (active) {
 #pragma unroll
                 for (int q = 0; q < kKP; ++q) {
-                    const float frt = f * sm.rt[s * p.SR + rr + q * p.R];
+                    const float rtv = rt[s * p.SR + rr + q * p.R];
                     float v[VEC], o[VEC];
-                    V16::unpack(raw[q], v);
+                    V16::unpack(raw[s & 1][q], v);
+                    const float2 rt2 = make_float2(rtv, rtv);
 #pragma unroll
-                    for (int j = 0; j < VEC; ++j) {
-                        const float e = kStash ? v[j] : ex2(fmaf(v[j], kLog2e, -ML));
-                        o[j] = e * (fax[j] + frt);
+                    for (int j = 0; j < VEC / 2; ++j) {
+                        const float2 a2 = __ffma2_rn(make_float2(v[2 * j], v[2 * j + 1]), l2e2, nML2);
+                        const float2 w2 = __fadd2_rn(make_float2(ax[2 * j], ax[2 * j + 1]), rt2);
+                        const float2 o2 = __fmul2_rn(make_float2(ex2(a2.x), ex2(a2.y)), w2);
+                        o[2 * j] = o2.x;
+                        o[2 * j + 1] = o2.y;
                     }
                     stg_stream(gdst + (long long)s * p.stage_bytes + q * p.pass_bytes, V16::pack(o));
                 }
             }
-            __syncwarp();
-            if (lane == 0) {
-                // the slot was written through the generic proxy (stash): order that before the
-                // producer's next bulk copy (async proxy) into it
-                fence_proxy_async();
-                mbar_arrive(smem_u32(&sm.empty[slot]));
-            }
         }
+        g += it.n;
+        // progress report for the reduce producer's L2-window throttle
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&sm.w_done[item_no % kRD]));
     }
 }
 
@@ -499,6 +595,15 @@ struct Geom {
     int G, R, SR, stage_bytes, pass_bytes, nact, NSv, P;
 };
 
+static int item_stages() {
+    int n = kDefItemStages;
+    if (const char* env = getenv("HIPE_RESIDENT_ITEM_STAGES")) {
+        const int v = atoi(env);
+        if (v >= 1 && v <= kMaxItemStages) n = v;
+    }
+    return n;
+}
+
 static bool pick_geom(int dtype, int D, int H, int W, Geom* g) {
     const int esz = dtype == HIPE_F32 ? 4 : 2;
     const long long row_b = (long long)W * esz;
@@ -508,7 +613,7 @@ static bool pick_geom(int dtype, int D, int H, int W, Geom* g) {
     if (NR >= (1ll << 30)) return false;
     for (int R = kC / G; R >= 1; --R) {
         const int SR = kKP * R;
-        if (SR > kMaxRtRows / kMaxItemStages) continue;
+        if (SR > kMaxRtRows / kDefItemStages) continue;
         if (2 * R * G < kC) break;   // fewer than half the consumers would work
         const bool ok = (SR % H == 0 && NR % SR == 0) || (H % SR == 0);
         if (!ok) continue;
@@ -517,7 +622,9 @@ static bool pick_geom(int dtype, int D, int H, int W, Geom* g) {
         g->stage_bytes = (int)(SR * row_b);
         g->nact = R * G;
         g->NSv = (int)(NR / SR);
-        g->P = (g->NSv + kMaxItemStages - 1) / kMaxItemStages;
+        int ist = item_stages();
+        if (ist * SR > kMaxRtRows) ist = kMaxRtRows / SR;
+        g->P = (g->NSv + ist - 1) / ist;
         return true;
     }
     return false;
@@ -567,14 +674,13 @@ extern "C" int hipe_joint_loss_resident(const void* logits, int dtype, long long
     if (major != 10) return HIPE_E_ARCH;
     if (!coop) return HIPE_E_UNSUPPORTED;
 
-    const bool stash = dtype == HIPE_F32;
-    const void* kern = stash ? (const void*)res::k_resident<float, true>
-                             : (const void*)res::k_resident<__nv_bfloat16, false>;
-    const size_t smem = (size_t)res::kSlots * res::kSlotBytes + sizeof(res::Smem);
+    const void* kern = dtype == HIPE_F32 ? (const void*)res::k_resident<float>
+                                         : (const void*)res::k_resident<__nv_bfloat16>;
+    const size_t smem = (size_t)(res::kRSlots + res::kWSlots) * res::kSlotBytes + sizeof(res::Smem);
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 2 * res::kC + 32, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, res::kThreads, smem);
     if (e != cudaSuccess) return (int)e;
     if (occ < 1) return HIPE_E_UNSUPPORTED;
     long long grid = (long long)sms;   // one CTA per SM: the ring takes the whole shared memory
@@ -593,6 +699,12 @@ extern "C" int hipe_joint_loss_resident(const void* logits, int dtype, long long
     p.W = W; p.H = H; p.D = D;
     p.G = g.G; p.R = g.R; p.SR = g.SR; p.stage_bytes = g.stage_bytes; p.pass_bytes = g.pass_bytes;
     p.nact = g.nact; p.NSv = g.NSv; p.P = g.P;
+    // L2 window = grid * lag * (<= 128 KB): 57 MB at the default, inside the 126 MB L2
+    p.lag = 3;
+    if (const char* env = getenv("HIPE_RESIDENT_LAG")) {
+        const int v = atoi(env);
+        if (v >= 1 && v <= res::kMaxLag) p.lag = v;
+    }
     p.coords = coords; p.expect = expect; p.stats = stats; p.loss_terms = loss_terms;
     p.gt = gt; p.vis = vis; p.tgt_f64 = (tgt_dtype == HIPE_F64); p.norm = norm;
     const size_t cb = res::ws_counters_bytes(n_vol);
@@ -605,7 +717,7 @@ extern "C" int hipe_joint_loss_resident(const void* logits, int dtype, long long
     e = cudaMemsetAsync(workspace, 0, cb, st);
     if (e != cudaSuccess) return (int)e;
     void* args[] = {(void*)&p};
-    e = cudaLaunchCooperativeKernel(kern, dim3((unsigned)grid), dim3(2 * res::kC + 32), args, smem, st);
+    e = cudaLaunchCooperativeKernel(kern, dim3((unsigned)grid), dim3(res::kThreads), args, smem, st);
     if (e == cudaErrorCooperativeLaunchTooLarge) {
         (void)cudaGetLastError();
         return HIPE_E_UNSUPPORTED;

@@ -50,6 +50,13 @@ def main():
         peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     except Exception:
         pass
+    if "resident" in a.ops:
+        med, mn = timeit(lambda: ops.joint_loss_resident(x, n_vol, D, D, D, gt, vis, 1.0 / a.B))
+        print(json.dumps({"op": "resident", "B": a.B, "dim": D, "dtype": a.dtype, "ms": round(med, 4), "min_ms": round(mn, 4),
+                          "GBs_2V": round(2 * n_vol * V * esz / med / 1e6, 1), "Mvol_s": round(n_vol / med / 1e3, 3),
+                          "env": {k: v for k, v in os.environ.items() if k.startswith("HIPE_")}}), flush=True)
+        if a.ops == "resident":
+            return
     for variant in [int(v) for v in a.variants.split(",")]:
         for cl in [int(c) for c in a.clusters.split(",")]:
             c, e, s = ops.softargmax_forward(x, n_vol, D, D, D, cluster=cl, variant=variant)
