@@ -38,6 +38,7 @@ namespace hipe {
 
 constexpr int kConsumers = 256;                   // consumer threads per CTA
 constexpr int kPasses = 4;                        // 16-byte vectors per thread per stage
+constexpr int kNSums = 5;                         // S0 Sx Sy Sz S0c
 constexpr int kStages = 4;                        // TMA ring depth
 constexpr int kStageBytes = kPasses * kConsumers * 16;  // 16 KB
 constexpr int kMaxCluster = 16;                  // 16 is non-portable (opt-in attribute), used by the resident fused launch
@@ -85,11 +86,11 @@ struct SmemLayout {
     // dynamic shared memory: [stages][kStageBytes] then this struct
     unsigned long long full[kStages];
     unsigned long long empty[kStages];
-    double wred[kConsumers / 32][4];
+    double wred[kConsumers / 32][kNSums];
     float wmax[kConsumers / 32];
-    double part[4];                // this CTA's partial (S0, Sx, Sy, Sz), read by peers through DSMEM
+    double part[kNSums];           // this CTA's partial (S0, Sx, Sy, Sz, S0c), read by peers through DSMEM
     float part_m;                  // ... and the maximum it is relative to
-    double all[kMaxCluster][4];
+    double all[kMaxCluster][kNSums];
     float all_m[kMaxCluster];
     double finE[3];                // Ex, Ey, Ez (voxel units)
     float fin[5];                  // M, L, gx, gy, gz

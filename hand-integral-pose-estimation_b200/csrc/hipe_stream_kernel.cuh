@@ -28,18 +28,19 @@ template <bool kSoftmax>
 struct Acc {
     float m;    // running max (natural units)
     float mL;   // fl(m * log2e): the exponent offset every e of this thread is relative to
-    double s0;  // sum e
-    double sx;  // sum e * (x - xc)   (xc = centre of the thread's columns)
-    double sy;  // sum e * y
-    double sz;  // sum e * z
+    double s0;  // sum of the per-visit row sums rs            (denominator of Ey, Ez; L)
+    double sx;  // sum C_j * (x_j - xc)   (xc = centre of the thread's columns, C_j column sums)
+    double sy;  // sum rs * y
+    double sz;  // sum rs * z
+    double s0c; // sum C_j                                     (denominator of Ex)
     __device__ __forceinline__ void init() {
         m = kSoftmax ? kNegInf : 0.f;
         mL = kSoftmax ? kNegInf : 0.f;
-        s0 = sx = sy = sz = 0.0;
+        s0 = sx = sy = sz = s0c = 0.0;
     }
     __device__ __forceinline__ void scale(float f) {
         const double d = (double)f;
-        s0 *= d; sx *= d; sy *= d; sz *= d;
+        s0 *= d; sx *= d; sy *= d; sz *= d; s0c *= d;
     }
 };
 
@@ -52,27 +53,24 @@ __device__ __forceinline__ float rebase_weight(float m_from, float m_to) {
                                : ex2(__fsub_rn(__fmul_rn(m_from, kLog2e), __fmul_rn(m_to, kLog2e)));
 }
 
-// Pairwise (tree) sums over the N exponentials of one visit: sum e_j, and sum (j - c) e_j with
-// the weights centred at c = (N-1)/2.  Centring halves the magnitude the fp32 roundings act
-// on and the tree keeps them to log2(N) levels: the x expectation's error is set by these
-// roundings (weights up to N/2 voxels), the y/z ones only see re-weighting errors.
+// Pairwise (tree) sum over the N exponentials of one visit.  Every expectation is a ratio of
+// two fp64 sums built from the SAME rounded fp32 atoms, so an fp32 rounding only re-weights
+// voxels (error ~ eps * spread of the distribution, zero for a one-hot volume):
+//   Ey, Ez  atoms = per-visit row sums rs (a visit lies in one row):  Sy/S0, Sz/S0;
+//   Ex      atoms = per-thread column sums C_j kept in fp32 over kFlush stages and folded into
+//           fp64 with their exact column index:                      Sx/S0c.
+// (An earlier version rounded sum (j-c) e_j per visit on its own; that error is eps * N/2 voxels
+// whatever the spread, and a near-one-hot volume whose E sits within 0.005 voxel of the peak
+// missed the 1e-5 gradient gate by 4x: scripts/diag_resident.py.)
 template <int N, int TOTAL>
 struct VisitSums {
     __device__ __forceinline__ static float rs(const float* e) {
         return VisitSums<N / 2, TOTAL>::rs(e) + VisitSums<N / 2, TOTAL>::rs(e + N / 2);
     }
-    // `first` = index of e[0] inside the visit
-    __device__ __forceinline__ static float xs(const float* e, int first) {
-        return VisitSums<N / 2, TOTAL>::xs(e, first) + VisitSums<N / 2, TOTAL>::xs(e + N / 2, first + N / 2);
-    }
 };
 template <int TOTAL>
 struct VisitSums<2, TOTAL> {
     __device__ __forceinline__ static float rs(const float* e) { return e[0] + e[1]; }
-    __device__ __forceinline__ static float xs(const float* e, int first) {
-        const float c = 0.5f * (float)(TOTAL - 1);
-        return fmaf((float)(first + 1) - c, e[1], ((float)first - c) * e[0]);
-    }
 };
 
 // fp32 -> fp64 of a float without the conversion unit (F2F.F64.F32 shares the
@@ -120,6 +118,12 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
     const unsigned char* gsrc = t.src + (long long)(16 * NV) * tid;
     xc_out = (double)(cg * EPV) + 0.5 * (double)(EPV - 1);
     a.init();
+    // column sums of this thread, fp32 for kFlush stages at a time (softmax terms are in [0, 1]:
+    // 8 stages x KP visits = 16-32 additions per column between folds)
+    constexpr int kFlush = kSoftmax ? 8 : 1;
+    float col[EPV];
+#pragma unroll
+    for (int j = 0; j < EPV; ++j) col[j] = 0.f;
 
     for (int i = 0; i < t.nst; ++i, ++it) {
         float v[KP][EPV];
@@ -175,7 +179,10 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
 #pragma unroll
                 for (int j = 0; j < EPV; ++j) smax = fmaxf(smax, v[q][j]);
             if (smax > a.m) {
-                a.scale(rebase_weight(a.m, smax));
+                const float wgt = rebase_weight(a.m, smax);
+                a.scale(wgt);
+#pragma unroll
+                for (int j = 0; j < EPV; ++j) col[j] *= wgt;
                 a.m = smax;
                 a.mL = __fmul_rn(smax, kLog2e);
             }
@@ -189,11 +196,10 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
 #pragma unroll
             for (int j = 0; j < EPV; ++j) e[j] = kSoftmax ? ex2(fmaf(v[q][j], kLog2e, -off)) : v[q][j];
             const float rs = VisitSums<EPV, EPV>::rs(e);
-            const float xs = VisitSums<EPV, EPV>::xs(e, 0);
+#pragma unroll
+            for (int j = 0; j < EPV; ++j) col[j] += e[j];
             const double drs = kSoftmax ? widen_nonneg(rs) : (double)rs;
-            const double dxs = kSoftmax ? widen_signed(xs) : (double)xs;
             a.s0 += drs;
-            a.sx += dxs;
             a.sy = fma(yd, drs, a.sy);
             a.sz = fma(zd, drs, a.sz);
             // next visited row: R = dz*H + dy rows further, one carry at most
@@ -202,6 +208,15 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
             if (yd >= Hd) {
                 yd -= Hd;
                 zd += 1.0;
+            }
+        }
+        if ((i + 1) % kFlush == 0 || i + 1 == t.nst) {
+#pragma unroll
+            for (int j = 0; j < EPV; ++j) {
+                const double dc = kSoftmax ? widen_nonneg(col[j]) : (double)col[j];
+                a.s0c += dc;
+                a.sx = fma((double)j - 0.5 * (double)(EPV - 1), dc, a.sx);
+                col[j] = 0.f;
             }
         }
     }
@@ -215,72 +230,74 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
 // ---------------------------------------------------------------------------------------
 template <bool kSoftmax>
 __device__ __forceinline__ void merge_partials(SmemLayout& sm, int tid, uint32_t S, const Acc<kSoftmax>& a,
-                                               double xc, double (&tot)[4], float& fm) {
+                                               double xc, double (&tot)[kNSums], float& fm) {
     const int lane = tid & 31, warp = tid >> 5;
-    double s0 = a.s0, sy = a.sy, sz = a.sz;
-    double sx = fma(xc, a.s0, a.sx);
+    // order: S0 (row-sum atoms), Sx, Sy, Sz, S0c (column-sum atoms)
+    double q[kNSums] = {a.s0, fma(xc, a.s0c, a.sx), a.sy, a.sz, a.s0c};
     float m = a.m;
     if constexpr (kSoftmax) {
         const float wm = warp_max(m);
         const double f = (double)rebase_weight(m, wm);
-        s0 *= f; sx *= f; sy *= f; sz *= f;
+#pragma unroll
+        for (int k = 0; k < kNSums; ++k) q[k] *= f;
         m = wm;
     }
-    s0 = warp_sum(s0); sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
+#pragma unroll
+    for (int k = 0; k < kNSums; ++k) q[k] = warp_sum(q[k]);
     if (lane == 0) {
-        sm.wred[warp][0] = s0; sm.wred[warp][1] = sx; sm.wred[warp][2] = sy; sm.wred[warp][3] = sz;
+#pragma unroll
+        for (int k = 0; k < kNSums; ++k) sm.wred[warp][k] = q[k];
         sm.wmax[warp] = m;
     }
     consumer_barrier();
     if (warp == 0) {
         constexpr int NW = kConsumers / 32;
         float pm = (lane < NW) ? sm.wmax[lane] : (kSoftmax ? kNegInf : 0.f);
-        double q0 = (lane < NW) ? sm.wred[lane][0] : 0.0;
-        double q1 = (lane < NW) ? sm.wred[lane][1] : 0.0;
-        double q2 = (lane < NW) ? sm.wred[lane][2] : 0.0;
-        double q3 = (lane < NW) ? sm.wred[lane][3] : 0.0;
+#pragma unroll
+        for (int k = 0; k < kNSums; ++k) q[k] = (lane < NW) ? sm.wred[lane][k] : 0.0;
         if constexpr (kSoftmax) {
             float wm = pm;
 #pragma unroll
             for (int o = NW / 2; o > 0; o >>= 1) wm = fmaxf(wm, __shfl_xor_sync(0xffffffffu, wm, o));
             const double f = (double)rebase_weight(pm, wm);
-            q0 *= f; q1 *= f; q2 *= f; q3 *= f;
+#pragma unroll
+            for (int k = 0; k < kNSums; ++k) q[k] *= f;
             pm = wm;
         }
 #pragma unroll
-        for (int o = NW / 2; o > 0; o >>= 1) {
-            q0 += __shfl_xor_sync(0xffffffffu, q0, o);
-            q1 += __shfl_xor_sync(0xffffffffu, q1, o);
-            q2 += __shfl_xor_sync(0xffffffffu, q2, o);
-            q3 += __shfl_xor_sync(0xffffffffu, q3, o);
-        }
+        for (int o = NW / 2; o > 0; o >>= 1)
+#pragma unroll
+            for (int k = 0; k < kNSums; ++k) q[k] += __shfl_xor_sync(0xffffffffu, q[k], o);
         if (lane == 0) {
-            sm.part[0] = q0; sm.part[1] = q1; sm.part[2] = q2; sm.part[3] = q3;
+#pragma unroll
+            for (int k = 0; k < kNSums; ++k) sm.part[k] = q[k];
             sm.part_m = pm;
         }
     }
     if (S > 1) {
         cluster_sync_all();  // every CTA's `part` is written and visible cluster-wide
-        if (tid < 4 * (int)S) sm.all[tid / 4][tid % 4] = dsmem_ld_f64(smem_u32(&sm.part[tid % 4]), tid / 4);
-        if (tid >= 32 && tid < 32 + (int)S) sm.all_m[tid - 32] = dsmem_ld_f32(smem_u32(&sm.part_m), tid - 32);
+        if (tid < kNSums * (int)S)
+            sm.all[tid / kNSums][tid % kNSums] = dsmem_ld_f64(smem_u32(&sm.part[tid % kNSums]), tid / kNSums);
+        if (tid >= 64 && tid < 64 + (int)S) sm.all_m[tid - 64] = dsmem_ld_f32(smem_u32(&sm.part_m), tid - 64);
         consumer_barrier();
         // done reading peers: arrive now, the caller waits before exiting
         asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     } else {
         consumer_barrier();
-        if (tid < 4) sm.all[0][tid] = sm.part[tid];
-        if (tid == 4) sm.all_m[0] = sm.part_m;
+        if (tid < kNSums) sm.all[0][tid] = sm.part[tid];
+        if (tid == 32) sm.all_m[0] = sm.part_m;
         consumer_barrier();
     }
     fm = kSoftmax ? kNegInf : 0.f;
-    tot[0] = tot[1] = tot[2] = tot[3] = 0.0;
+#pragma unroll
+    for (int k = 0; k < kNSums; ++k) tot[k] = 0.0;
     if (tid == 0) {
         if constexpr (kSoftmax)
             for (uint32_t r = 0; r < S; ++r) fm = fmaxf(fm, sm.all_m[r]);
         for (uint32_t r = 0; r < S; ++r) {
             const double f = kSoftmax ? (double)rebase_weight(sm.all_m[r], fm) : 1.0;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) tot[k] = fma(f, sm.all[r][k], tot[k]);
+            for (int k = 0; k < kNSums; ++k) tot[k] = fma(f, sm.all[r][k], tot[k]);
         }
     }
 }
@@ -474,12 +491,12 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
             reduce_pass<T, kTma, kSoftmax, 2>(p, t, smem_raw, sm, tid, it, a, xc);
         else
             reduce_pass<T, kTma, kSoftmax, 1>(p, t, smem_raw, sm, tid, it, a, xc);
-        double tot[4];
+        double tot[kNSums];
         float fm;
         merge_partials<kSoftmax>(sm, tid, S, a, xc, tot, fm);
         if (tid == 0) {
             // loss.py:39-41 (expectations) and :54-56 (normalisation), in fp64, rounded once
-            const double ex_ = kSoftmax ? tot[1] / tot[0] : tot[1];
+            const double ex_ = kSoftmax ? tot[1] / tot[4] : tot[1];
             const double ey_ = kSoftmax ? tot[2] / tot[0] : tot[2];
             const double ez_ = kSoftmax ? tot[3] / tot[0] : tot[3];
             const float cxn = (float)(ex_ / (double)p.W - 0.5);

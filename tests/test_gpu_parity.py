@@ -70,6 +70,47 @@ def test_backward_grads(geom, variant):
             "geom %s cluster %d: %.3e" % (geom, cluster, (np.abs(d - ref) / scale).max())
 
 
+def _near_one_hot(B, J, D, H, W, seed):
+    """Volumes whose mass sits in ONE voxel (p ~ 0.9-0.999) with E a few 1e-3 voxel off its centre:
+    the gradient at the peak is p * (idx - E) with idx - E ~ 1e-3, so any absolute error in E shows
+    up undiluted (the sharp-regime case that first missed the gate: scripts/diag_resident.py)."""
+    rng = np.random.default_rng(seed)
+    hm = rng.standard_normal((B * J, D, H, W)).astype(np.float32) * 0.5
+    for v in range(B * J):
+        z, y, x = rng.integers(1, D - 1), rng.integers(1, H - 1), rng.integers(1, W - 1)
+        peak = rng.uniform(14.0, 24.0)
+        hm[v, z, y, x] += peak
+        for dz, dy, dx in ((0, 0, 1), (0, 1, 0), (1, 0, 0), (0, 0, -1), (0, -1, 0), (-1, 0, 0)):
+            hm[v, z + dz, y + dy, x + dx] += peak - rng.uniform(4.0, 9.0)
+    return hm.reshape(B, J * D, H, W)
+
+
+@pytest.mark.parametrize("case", ["sharp5", "onehot"])
+@pytest.mark.parametrize("geom", [(64, 64, 64), (16, 16, 16), (12, 20, 24)])
+def test_backward_grads_when_E_sits_on_the_peak(geom, case):
+    from hipe_b200 import ops
+    D, H, W = geom
+    J, B = 21, 3
+    hm = synth.heatmaps(B, J, D, H, W, "sharp", seed=5) if case == "sharp5" else _near_one_hot(B, J, D, H, W, 17)
+    gt, vis = synth.targets(B, J, seed=5)
+    up = hm.astype(np.float64)
+    _, ref_c = O.joint_location_loss(up, gt, vis, return_coords=True)
+    ref = O.joint_location_loss_grad(up, gt, vis).reshape(B * J, -1)
+    scale = np.abs(ref).max(axis=1, keepdims=True)
+    x = _cuda(hm)
+    for cluster in [0, 1, 2, 4, 8]:
+        for variant in (1, 2):
+            c, e, s = ops.softargmax_forward(x, B * J, D, H, W, cluster=cluster, variant=variant)
+            err, ok = _coord_ok(c.view(B, 3 * J).cpu().numpy(), ref_c)
+            assert ok
+            _, g = ops.l1_loss(c.view(B, 3 * J), _cuda(gt), _cuda(vis), 1.0 / B)
+            d = ops.softargmax_backward(x, B * J, D, H, W, s, e, g.view(-1, 3), cluster=cluster, variant=variant)
+            d = d.cpu().numpy().reshape(B * J, -1).astype(np.float64)
+            rel = np.abs(d - ref) / scale
+            assert (np.abs(d - ref) <= 1e-5 * scale + 1e-12).all(), \
+                "geom %s %s cluster %d variant %d: %.3e" % (geom, case, cluster, variant, rel.max())
+
+
 @pytest.mark.parametrize("fused", [False, True])
 @pytest.mark.parametrize("tgt", [np.float64, np.float32])
 @pytest.mark.parametrize("geom", [(16, 16, 16), (64, 64, 64), (5, 6, 7)])
@@ -113,7 +154,11 @@ def test_upstream_gradient_scaling_fused_and_unfused():
     x = _cuda(hm).requires_grad_(True)
     L.JointLocationLoss()(x, _cuda(gt), _cuda(vis)).backward()
     torch.testing.assert_close(grads[0], 0.25 * x.grad, rtol=1e-6, atol=0)
-    torch.testing.assert_close(grads[1], 0.25 * x.grad, rtol=1e-5, atol=1e-12)
+    # the fused launch is a different kernel (its own summation order): compare against the
+    # per-volume gradient scale, the way the parity gate is defined, not element-relative
+    want = (0.25 * x.grad).view(B * J, -1)
+    scale = want.abs().amax(dim=1, keepdim=True)
+    assert ((grads[1].view(B * J, -1) - want).abs() <= 5e-6 * scale + 1e-12).all()
 
 
 def test_bf16_forward_backward():
