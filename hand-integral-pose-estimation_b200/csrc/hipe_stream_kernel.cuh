@@ -12,6 +12,17 @@
 #pragma once
 #include "hipe_common.cuh"
 
+// Resident CTAs per SM the TMA kernels are compiled for (register cap 65536 / (288 * n)).
+// Measured on B200 (scripts/ab_minctas.sh): the reduce-only launches like 3 CTAs of <= 72
+// registers (bf16 forward 5.24 vs 5.16 TB/s); the launches with a write pass are 1-9 % faster
+// with 2 CTAs and no spills (bf16 backward 6.67 vs 6.45 TB/s, fused 56^3 0.566 vs 0.618 ms).
+#ifndef HIPE_MIN_CTAS_REDUCE
+#define HIPE_MIN_CTAS_REDUCE 3
+#endif
+#ifndef HIPE_MIN_CTAS_WRITE
+#define HIPE_MIN_CTAS_WRITE 2
+#endif
+
 namespace hipe {
 
 // geometry of one CTA's share of its volume (uniform over the CTA)
@@ -62,15 +73,18 @@ __device__ __forceinline__ float rebase_weight(float m_from, float m_to) {
 // (An earlier version rounded sum (j-c) e_j per visit on its own; that error is eps * N/2 voxels
 // whatever the spread, and a near-one-hot volume whose E sits within 0.005 voxel of the peak
 // missed the 1e-5 gradient gate by 4x: scripts/diag_resident.py.)
-template <int N, int TOTAL>
-struct VisitSums {
-    __device__ __forceinline__ static float rs(const float* e) {
-        return VisitSums<N / 2, TOTAL>::rs(e) + VisitSums<N / 2, TOTAL>::rs(e + N / 2);
+// Blackwell packed fp32: one FFMA2 / FADD2 / FMUL2 issue slot does two lanes' worth of work.  The
+// reduce pass is issue-bound for bf16 logits (ncu: 75 % issue, 70 % XU at 60 % of HBM), so the
+// scale-and-offset, the column sums and the per-visit tree sum all run on float2 pairs.
+template <int NP>
+struct PairTree {   // sum of NP float2 values, pairwise
+    __device__ __forceinline__ static float2 sum(const float2* a) {
+        return __fadd2_rn(PairTree<NP / 2>::sum(a), PairTree<NP / 2>::sum(a + NP / 2));
     }
 };
-template <int TOTAL>
-struct VisitSums<2, TOTAL> {
-    __device__ __forceinline__ static float rs(const float* e) { return e[0] + e[1]; }
+template <>
+struct PairTree<1> {
+    __device__ __forceinline__ static float2 sum(const float2* a) { return a[0]; }
 };
 
 // fp32 -> fp64 of a float without the conversion unit (F2F.F64.F32 shares the
@@ -112,8 +126,10 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
     const int full = nvis / KP;              // stages whose KP visits are all inside the range
     const int pass_bytes = R * t.row_bytes;
     const int row_first = t.r0 + rr;
-    double yd = (double)(row_first % p.H), zd = (double)(row_first / p.H);
-    const double dyd = (double)(R % p.H), dzd = (double)(R / p.H), Hd = (double)p.H;
+    // row coordinates of the current visit: small integers, exact in fp32 (FADD/FSETP instead of
+    // fp64 adds and int->double conversions, which share the XU pipe with MUFU.EX2)
+    float yf = (float)(row_first % p.H), zf = (float)(row_first / p.H);
+    const float dyf = (float)(R % p.H), dzf = (float)(R / p.H), Hf = (float)p.H;
     const uint32_t lds_base = kTma ? smem_u32(smem_raw) + (uint32_t)(16 * NV) * tid : 0u;
     const unsigned char* gsrc = t.src + (long long)(16 * NV) * tid;
     xc_out = (double)(cg * EPV) + 0.5 * (double)(EPV - 1);
@@ -121,9 +137,10 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
     // column sums of this thread, fp32 for kFlush stages at a time (softmax terms are in [0, 1]:
     // 8 stages x KP visits = 16-32 additions per column between folds)
     constexpr int kFlush = kSoftmax ? 8 : 1;
-    float col[EPV];
+    constexpr int NP = EPV / 2;
+    float2 col[NP];
 #pragma unroll
-    for (int j = 0; j < EPV; ++j) col[j] = 0.f;
+    for (int j = 0; j < NP; ++j) col[j] = make_float2(0.f, 0.f);
 
     for (int i = 0; i < t.nst; ++i, ++it) {
         float v[KP][EPV];
@@ -182,7 +199,7 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
                 const float wgt = rebase_weight(a.m, smax);
                 a.scale(wgt);
 #pragma unroll
-                for (int j = 0; j < EPV; ++j) col[j] *= wgt;
+                for (int j = 0; j < NP; ++j) col[j] = __fmul2_rn(col[j], make_float2(wgt, wgt));
                 a.m = smax;
                 a.mL = __fmul_rn(smax, kLog2e);
             }
@@ -190,34 +207,46 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
         // all -inf so far: exponentiate against 0 so that e = 2^-inf = 0 (no NaN, no branch)
         const float off = (kSoftmax && a.m == kNegInf) ? 0.f : a.mL;
         // ---- accumulate: fp32 inside one visit, fp64 across visits ----
+        const float2 sc2 = make_float2(kLog2e, kLog2e), off2 = make_float2(-off, -off);
 #pragma unroll
         for (int q = 0; q < KP; ++q) {
-            float e[EPV];
+            float2 e[NP];
 #pragma unroll
-            for (int j = 0; j < EPV; ++j) e[j] = kSoftmax ? ex2(fmaf(v[q][j], kLog2e, -off)) : v[q][j];
-            const float rs = VisitSums<EPV, EPV>::rs(e);
+            for (int j = 0; j < NP; ++j) {
+                const float2 x = make_float2(v[q][2 * j], v[q][2 * j + 1]);
+                if constexpr (kSoftmax) {
+                    const float2 a2 = __ffma2_rn(x, sc2, off2);
+                    e[j] = make_float2(ex2(a2.x), ex2(a2.y));
+                } else {
+                    e[j] = x;
+                }
+            }
+            const float2 r2 = PairTree<NP>::sum(e);
+            const float rs = r2.x + r2.y;
 #pragma unroll
-            for (int j = 0; j < EPV; ++j) col[j] += e[j];
+            for (int j = 0; j < NP; ++j) col[j] = __fadd2_rn(col[j], e[j]);
             const double drs = kSoftmax ? widen_nonneg(rs) : (double)rs;
             a.s0 += drs;
-            a.sy = fma(yd, drs, a.sy);
-            a.sz = fma(zd, drs, a.sz);
+            a.sy = fma(widen_nonneg(yf), drs, a.sy);
+            a.sz = fma(widen_nonneg(zf), drs, a.sz);
             // next visited row: R = dz*H + dy rows further, one carry at most
-            yd += dyd;
-            zd += dzd;
-            if (yd >= Hd) {
-                yd -= Hd;
-                zd += 1.0;
+            yf += dyf;
+            zf += dzf;
+            if (yf >= Hf) {
+                yf -= Hf;
+                zf += 1.f;
             }
         }
         if ((i + 1) % kFlush == 0 || i + 1 == t.nst) {
 #pragma unroll
             for (int j = 0; j < EPV; ++j) {
-                const double dc = kSoftmax ? widen_nonneg(col[j]) : (double)col[j];
+                const float cj = (j & 1) ? col[j / 2].y : col[j / 2].x;
+                const double dc = kSoftmax ? widen_nonneg(cj) : (double)cj;
                 a.s0c += dc;
                 a.sx = fma((double)j - 0.5 * (double)(EPV - 1), dc, a.sx);
-                col[j] = 0.f;
             }
+#pragma unroll
+            for (int j = 0; j < NP; ++j) col[j] = make_float2(0.f, 0.f);
         }
     }
 }
@@ -408,7 +437,7 @@ __device__ __forceinline__ void write_pass(const Params& p, const Tile& t, unsig
 // reduce + L1 gradient + write in one launch (fused).
 // ---------------------------------------------------------------------------------------
 template <typename T, bool kTma, int kOp>
-__global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers)
+__global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers, !kTma ? 1 : ((kOp == OP_REDUCE_SOFTMAX || kOp == OP_REDUCE_PLAIN) ? HIPE_MIN_CTAS_REDUCE : HIPE_MIN_CTAS_WRITE))
     k_stream(const Params p) {
     constexpr bool kHasReduce = (kOp == OP_REDUCE_SOFTMAX || kOp == OP_REDUCE_PLAIN || kOp == OP_FUSED);
     constexpr bool kHasWrite = (kOp == OP_WRITE_GRAD || kOp == OP_WRITE_PROB || kOp == OP_FUSED);

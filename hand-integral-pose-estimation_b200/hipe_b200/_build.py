@@ -38,6 +38,7 @@ def build(force=False, verbose=False):
     if not force and not needs_build():
         return LIB_PATH
     flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
+    flags += os.environ.get("HIPE_NVCC_EXTRA", "").split()   # tuning experiments only (-DHIPE_MIN_CTAS=2 ...)
     objs = []
     procs = []
     for s in SOURCES:

@@ -158,6 +158,34 @@ def procrustes_cases():
     return out
 
 
+def chain_case():
+    """data/FreiHand/FreiHand.py:683-767 (labelled split: R, Procrustes) and :853-883 (evaluation
+    split: trans from the box, no R) per sample through the live reference functions."""
+    ch = ref_loader.load_chain_functions()
+    cst = ref_loader.load_compute_similarity_transform()
+    c = synth.chain_inputs(48, seed=301)
+    N = len(c["tprime"])
+    out = dict(c)
+    trans = np.array([ch.gen_trans_from_patch_cv(*c["bbox"][i], 224, 224, 1.0, inv=True) for i in range(N)])
+    out["trans"] = trans
+    img, cam, cam_norot, Z = [], [], [], []
+    for i in range(N):
+        pim = ch.trans_coords_from_patch_to_org_3d(c["patch"][i].copy(), *c["bbox"][i], 224, 224, 1.0,
+                                                   trans[i], c["tprime"][i])
+        img.append(pim.copy())
+        p3 = ch.pixel2cam(pim[:, 0:3].copy(), c["K"][i])
+        e, _ = ch.scale_result(None, p3, method="scale", bone_length=float(c["bone_len"][i]))
+        cam_norot.append(e)                                     # FreiHand.py:879-883
+        p3r = np.matmul(c["R"][i].T, p3.T).T                    # FreiHand.py:722
+        p3r, _ = ch.scale_result(None, p3r, method="scale", bone_length=float(c["bone_len"][i]))
+        cam.append(p3r)
+        Z.append(cst(c["gt_cam"][i], p3r, compute_optimal_scale=True)[1])
+    out["img"], out["cam"], out["cam_norot"], out["Z"] = map(np.array, (img, cam, cam_norot, Z))
+    out["pa_mpjpe"] = np.array(np.mean(np.sqrt(np.sum((out["Z"] - c["gt_cam"]) ** 2, axis=2))))
+    out["mpjpe"] = np.array(np.mean(np.sqrt(np.sum((out["cam"] - c["gt_cam"]) ** 2, axis=2))))
+    return out
+
+
 def main():
     if not ref_loader.available():
         raise SystemExit("the reference tree is not mounted; goldens can only be made in the build container")
@@ -167,6 +195,11 @@ def main():
         np.savez_compressed(os.path.join(HERE, "integral_%s.npz" % name), **d)
         print(name, "loss64 %.12f" % d["loss64"], "|c32-c64| max %.2e" % np.abs(d["coords32"] - d["coords64"]).max())
     np.savez_compressed(os.path.join(HERE, "combined_cube8.npz"), **combined_case(L))
+    ch = chain_case()
+    np.savez_compressed(os.path.join(HERE, "chain.npz"), **ch)
+    print("chain PA-MPJPE %.6f m, MPJPE %.6f m" % (ch["pa_mpjpe"], ch["mpjpe"]))
+    if "--chain-only" in sys.argv:
+        return
     p = procrustes_cases()
     np.savez_compressed(os.path.join(HERE, "procrustes.npz"), **p)
     print("freihand PA-MPJPE %.6f m, MPJPE %.6f m" % (p["freihand_pa_mpjpe"], p["freihand_mpjpe"]))

@@ -98,6 +98,26 @@ def load_eval_module():
     return _cache["eval"]
 
 
+def load_chain_functions():
+    """The coordinate chain between soft-argmax and Procrustes: source slices
+    of common/augment.py (pixel2cam :89-103, trans_coords_from_patch_to_org{,_3d} :186-217,
+    gen_trans_from_patch_cv + trans_point2d :457-511) and FreiHand.scale_result
+    (data/FreiHand/FreiHand.py:632-668, a method: dedented and called with self=None)."""
+    if "chain" not in _cache:
+        import textwrap
+        import cv2
+        import numpy as np
+        ns = {"np": np, "cv2": cv2}
+        exec(_slice("common/augment.py", 89, 103), ns)
+        exec(_slice("common/augment.py", 186, 217), ns)
+        exec(_slice("common/augment.py", 457, 511), ns)
+        exec(textwrap.dedent(_slice("data/FreiHand/FreiHand.py", 632, 668)), ns)
+        _cache["chain"] = types.SimpleNamespace(
+            pixel2cam=ns["pixel2cam"], trans_coords_from_patch_to_org_3d=ns["trans_coords_from_patch_to_org_3d"],
+            gen_trans_from_patch_cv=ns["gen_trans_from_patch_cv"], scale_result=ns["scale_result"])
+    return _cache["chain"]
+
+
 def fixture_arrays():
     """The two joint-set arrays the reference ships."""
     import numpy as np

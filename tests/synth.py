@@ -56,3 +56,36 @@ def procrustes_pairs(n, J=21, seed=0, noise=0.005, mirror_frac=0.0):
         m = rng.uniform(size=n) < mirror_frac
         X[m, :, 0] *= -1.0
     return X, Y
+
+
+def chain_inputs(n, J=21, seed=0, patch=224.0):
+    """Per-sample inputs of the patch -> camera chain (data/FreiHand/FreiHand.py:683-742) with
+    FreiHAND-like magnitudes: a hand 0.5-1 m away, 224x224 images, focal length ~ 480 px.
+    Ground truth in camera space is projected into a box crop to make consistent patch
+    coordinates, which are then perturbed (the 'prediction')."""
+    rng = np.random.default_rng(seed)
+    gt_cam = hand_like_joints(n, J, seed + 3)
+    R = random_rotations(n, rng)
+    K = np.zeros((n, 3, 3))
+    K[:, 0, 0] = rng.uniform(440, 520, n)
+    K[:, 1, 1] = K[:, 0, 0] * rng.uniform(0.98, 1.02, n)
+    K[:, 0, 2] = rng.uniform(100, 124, n)
+    K[:, 1, 2] = rng.uniform(100, 124, n)
+    K[:, 2, 2] = 1.0
+    K[:, 0, 1] = rng.uniform(-0.5, 0.5, n)              # a little skew: exercises the full inverse
+    rot = np.einsum("nik,njk->nji", R, gt_cam)          # (R x^T)^T
+    uvw = np.einsum("nik,njk->nji", K, rot)
+    uv = uvw[..., :2] / uvw[..., 2:3]
+    z_mm = rot[..., 2] * 1000.0
+    lo, hi = uv.min(axis=1), uv.max(axis=1)
+    ctr = 0.5 * (lo + hi)
+    size = (hi - lo).max(axis=1) * rng.uniform(1.2, 1.6, n)
+    bbox = np.stack([ctr[:, 0], ctr[:, 1], size, size * rng.uniform(0.9, 1.1, n)], axis=1)
+    tprime = z_mm[:, 9] + rng.uniform(-5, 5, n)
+    x = (uv[..., 0] - (bbox[:, None, 0] - 0.5 * bbox[:, None, 2])) * patch / bbox[:, None, 2]
+    y = (uv[..., 1] - (bbox[:, None, 1] - 0.5 * bbox[:, None, 3])) * patch / bbox[:, None, 3]
+    z = z_mm - tprime[:, None]
+    pt = np.stack([x, y, z, np.ones_like(x)], axis=2)
+    pt[..., 0:3] += rng.standard_normal((n, J, 3)) * np.array([2.0, 2.0, 4.0])
+    bone = np.sqrt(((gt_cam[:, 9] - gt_cam[:, 10]) ** 2).sum(axis=1))
+    return {"patch": pt, "bbox": bbox, "tprime": tprime, "K": K, "R": R, "bone_len": bone, "gt_cam": gt_cam}
