@@ -1,6 +1,7 @@
 """Drop-in for the hot-path functions of the reference's common/augment.py:
-`compute_similarity_transform` (:18-77) and `get_joint_location_result` (:160-184), running
-on the sm_100a kernels.  The reference's image/patch augmentation code is out of scope."""
+`compute_similarity_transform` (:18-77), `get_joint_location_result` (:160-184) and the
+per-sample coordinate chain `trans_coords_from_patch_to_org_3d` (:196-217) / `pixel2cam`
+(:89-103), running on the sm_100a kernels.  The reference's image/patch augmentation code is out of scope."""
 import numpy as np
 import torch
 
@@ -37,3 +38,34 @@ def get_joint_location_result(patch_width, patch_height, preds):
     coords[:, :, 2] = coords[:, :, 2] * patch_width
     scores = np.ones((coords.shape[0], coords.shape[1], 1), dtype=float)
     return np.concatenate((coords, scores), axis=2)
+
+
+def _one(a, shape):
+    return torch.as_tensor(np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(shape))).cuda()
+
+
+def trans_coords_from_patch_to_org_3d(coords_in_patch, c_x, c_y, bb_width, bb_height, patch_width, patch_height,
+                                      scale, trans, tprime, p=False):
+    """augment.py:196-217 for one (J, C>=3) sample, numpy in / numpy out (same positional
+    signature; like the reference only `trans` and `tprime` enter the arithmetic)."""
+    c = np.asarray(coords_in_patch, dtype=np.float64)
+    J = c.shape[0]
+    K = np.eye(3)[None]
+    o = _ev.camera_joints(_one(c, (1, J, c.shape[1])), _one(tprime, (1,)), _one(K, (1, 3, 3)),
+                          trans=_one(trans, (1, 3, 3)), num_joints=J, want=("img",))
+    out = c.copy()
+    out[:, 0:3] = o["img"][0].cpu().numpy()
+    return out
+
+
+def pixel2cam(pixel_coord, K, pp=False):
+    """augment.py:89-103 for one (J, 3) sample: K^-1 (u, v, 1) z / 1000.  (The reference also
+    divides the caller's z column by 1000 in place; so does this.)"""
+    pc = np.asarray(pixel_coord, dtype=np.float64)
+    J = pc.shape[0]
+    ident = np.array([[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.0, 0.0, 1.0]])
+    o = _ev.camera_joints(_one(pc, (1, J, 3)), _one(0.0, (1,)), _one(K, (1, 3, 3)), trans=_one(ident, (1, 3, 3)),
+                          num_joints=J, want=("cam",))
+    if isinstance(pixel_coord, np.ndarray) and pixel_coord.dtype.kind == "f":
+        pixel_coord[..., 2] = pixel_coord[..., 2] / 1000
+    return o["cam"][0].cpu().numpy()

@@ -31,6 +31,14 @@ SIGNATURES = {
     "hipe_scale_inplace": (_i, [_vp, _i, _ll, _vp, _vp]),
     "hipe_sum_f64": (_i, [_vp, _ll, _d, _vp, _vp]),
     "hipe_procrustes_batched": (_i, [_vp, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "hipe_patch_to_camera": (_i, [_vp, _i, _i, _ll, _i, _d, _d, _vp, _vp, _d, _d, _d, _vp, _vp, _vp, _vp, _i, _i,
+                                  _vp, _vp, _vp]),
+    "hipe_eval_chain_procrustes": (_i, [_vp, _i, _i, _ll, _i, _d, _d, _vp, _vp, _d, _d, _d, _vp, _vp, _vp, _vp, _i,
+                                        _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "hipe_keypoint_measures_workspace_bytes": (_ll, [_i, _i]),
+    "hipe_keypoint_measures": (_i, [_vp, _vp, _ll, _i, _d, _d, _i, _vp, _vp, _vp, _ll, _vp]),
+    "hipe_orthonormalize3_fwd": (_i, [_vp, _i, _ll, _vp, _vp, _vp]),
+    "hipe_orthonormalize3_bwd": (_i, [_vp, _i, _ll, _vp, _vp, _vp]),
     "hipe_joint_location_loss_host": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp,
                                            _vp, _ll]),
     "hipe_procrustes_host": (_i, [_vp, _vp, _ll, _i, _i, _i, _vp, _vp, _vp]),

@@ -51,21 +51,46 @@ def pa_mpjpe(gt, pred, device=None, mode=MODE_SIMILARITY):
     return ops.sum_f64(o["pa_dist"], 1.0 / n), ops.sum_f64(o["raw_dist"], 1.0 / n), o["Z"]
 
 
-def keypoint_measures(dist, val_min=0.0, val_max=0.05, steps=100):
-    """main/eval.py:25-106 (EvalUtil.feed + get_measures) from per-keypoint distances (N,K) on the
-    device: mean/median EPE per keypoint, PCK over linspace thresholds, trapezoid AUC, then the
-    means over keypoints.  Returns (epe_mean, epe_median, auc, pck_curve, thresholds)."""
-    d = dist.to(torch.float64)
-    thr = torch.linspace(val_min, val_max, steps, dtype=torch.float64, device=d.device)
-    pck = (d.unsqueeze(-1) <= thr).to(torch.float64).mean(dim=0)            # (K, steps)
-    span = torch.trapezoid(torch.ones_like(thr), thr)
-    auc = torch.trapezoid(pck, thr, dim=1) / span
-    return d.mean(dim=0).mean(), d.median(dim=0).values.mean() if d.shape[0] % 2 else _median_even(d).mean(), \
-        auc.mean(), pck.mean(dim=0), thr
+def camera_joints(coords, tprime, K, trans=None, bbox=None, R=None, bone_len=None, num_joints=21,
+                  patch=(224.0, 224.0), dst=(224.0, 224.0), want=("cam",)):
+    """Soft-argmax output (B, 3J) float32 -- or patch pixels (B, J, 3|4) -- to camera-space joints in
+    metres: get_joint_location_result's rescale, trans_coords_from_patch_to_org_3d, pixel2cam, R^T
+    and the bone-length rescale (common/augment.py:89-103,176-217; data/FreiHand/FreiHand.py:632-653,
+    722), one launch, nothing leaves the device.  Returns a dict with the tensors named in `want`
+    ("img" = image-space (u, v, z_mm), "cam")."""
+    if not isinstance(coords, torch.Tensor):
+        coords = torch.as_tensor(np.ascontiguousarray(coords, dtype=np.float64)).to(_dev())
+    N = coords.shape[0]
+    return ops.patch_to_camera(coords, N, num_joints, tprime, K, trans=trans, bbox=bbox, R=R, bone_len=bone_len,
+                               patch=patch, dst=dst, want=want)
 
 
-def _median_even(d):
-    # np.median averages the two middle values for even counts; torch.median takes the lower
-    s, _ = torch.sort(d, dim=0)
-    n = d.shape[0]
-    return 0.5 * (s[n // 2 - 1] + s[n // 2])
+def evaluate_chain(coords, gt_cam, tprime, K, trans=None, bbox=None, R=None, bone_len=None, num_joints=21,
+                   patch=(224.0, 224.0), dst=(224.0, 224.0), mode=MODE_SIMILARITY):
+    """The per-sample body of FreiHand.evaluate (data/FreiHand/FreiHand.py:703-767,804-807) for a whole
+    batch in one launch: chain -> Procrustes -> per-joint distances.  Returns (PA-MPJPE, MPJPE) as
+    0-dim CUDA fp64 tensors and a dict with cam, Z, pa_dist, raw_dist."""
+    if not isinstance(coords, torch.Tensor):
+        coords = torch.as_tensor(np.ascontiguousarray(coords, dtype=np.float64)).to(_dev())
+    N = coords.shape[0]
+    o = ops.patch_to_camera(coords, N, num_joints, tprime, K, trans=trans, bbox=bbox, R=R, bone_len=bone_len,
+                            patch=patch, dst=dst, gt=gt_cam, mode=mode, optimal_scale=True,
+                            want=("cam", "Z", "pa_dist", "raw_dist"))
+    n = o["pa_dist"].numel()
+    return ops.sum_f64(o["pa_dist"], 1.0 / n), ops.sum_f64(o["raw_dist"], 1.0 / n), o
+
+
+def keypoint_measures(dist, val_min=0.0, val_max=0.05, steps=100, vis=None, per_keypoint=False):
+    """main/eval.py:25-106 (EvalUtil.feed + get_measures) from per-keypoint distances (N, K) on the
+    device, one launch pair (hipe_keypoint_measures): mean / median EPE per keypoint, PCK over the
+    linspace thresholds, trapezoid AUC, then the means over the keypoints that were fed.
+    `vis` (N, K), optional: only entries with vis != 0 are fed (main/eval.py:45-47).
+    Returns (epe_mean, epe_median, auc, pck_curve, thresholds) as CUDA fp64 tensors; with
+    per_keypoint=True also a dict of the per-keypoint count / mean / median / auc / pck."""
+    if not isinstance(dist, torch.Tensor):
+        dist = torch.as_tensor(np.ascontiguousarray(dist, dtype=np.float64)).to(_dev())
+    out = ops.keypoint_measures(dist, val_min, val_max, steps, vis)
+    # np.linspace's own roundings (torch.linspace differs in the last bit); the kernel forms the same values
+    thr = torch.as_tensor(np.linspace(val_min, val_max, steps)).to(dist.device)
+    res = (out["summary"][0], out["summary"][1], out["summary"][2], out["pck_curve"], thr)
+    return res + (out["per_keypoint"],) if per_keypoint else res

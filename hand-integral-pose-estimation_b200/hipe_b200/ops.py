@@ -162,8 +162,24 @@ def sum_f64(x, scale=1.0):
     return out
 
 
-# "auto": the persistent on-chip launch whenever the geometry allows it, else the L2 re-read launch
+# "auto": the launch measured fastest for the geometry (fused_plan); "resident" / "stream" force one
 FUSED_MODE = "auto"          # "auto" | "resident" | "stream"
+
+
+def fused_plan(logits, n_vol, D, H, W):
+    """Which launch computes loss + gradient fastest for this geometry, from B200 measurements
+    (profiles/r1_configs.md): "resident" (persistent on-chip launch, one HBM read + one write)
+    for the fp32 geometry it is tuned for -- 256-byte rows, volumes <= 1 MiB, i.e. 21x64^3;
+    "stream" (one launch, second read from L2) for other fp32 volumes; None = the two-launch
+    forward + recompute backward (bf16: the fused launches gain < 4 % or lose)."""
+    if logits.dtype != torch.float32:
+        return None
+    vol_bytes = D * H * W * 4
+    if W * 4 == 256 and vol_bytes <= (1 << 20) and n_vol >= 296 and resident_supported(logits, n_vol, D, H, W):
+        return "resident"
+    if (W * 4) % 16 == 0 and vol_bytes >= (1 << 19):
+        return "stream"
+    return None
 _WORKSPACES = {}             # (device index, stream) -> uint8 scratch tensor, grown on demand
 
 
@@ -225,7 +241,7 @@ def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, varian
     _need_cuda(logits, "heatmaps")
     mode = FUSED_MODE if mode is None else mode
     if mode == "resident" or (mode == "auto" and cluster is None and variant is None
-                              and resident_supported(logits, n_vol, D, H, W)):
+                              and fused_plan(logits, n_vol, D, H, W) == "resident"):
         try:
             return joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm)
         except _lib.HipeError as e:
@@ -271,6 +287,96 @@ def procrustes(X, Y, mode=0, optimal_scale=True, want=("Z", "pa_dist", "raw_dist
             X.data_ptr(), Y.data_ptr(), N, J, int(mode), 1 if optimal_scale else 0,
             _ptr(out.get("d")), _ptr(out.get("Z")), _ptr(out.get("T")), _ptr(out.get("b")),
             _ptr(out.get("c")), _ptr(out.get("pa_dist")), _ptr(out.get("raw_dist")), _stream(X)))
+    return out
+
+
+def keypoint_measures(dist, val_min, val_max, steps, vis=None):
+    """hipe_keypoint_measures on a CUDA (N, K) distance matrix; see evaluate.keypoint_measures."""
+    _need_cuda(dist, "dist")
+    d = dist.to(torch.float64).contiguous()
+    if d.dim() != 2:
+        raise ValueError("dist must be (N, K)")
+    N, K = d.shape
+    v = None
+    if vis is not None:
+        if not isinstance(vis, torch.Tensor):
+            import numpy as np
+            vis = torch.as_tensor(np.ascontiguousarray(vis))
+        v = (vis.to(d.device) != 0).to(torch.uint8).contiguous()
+        if tuple(v.shape) != (N, K):
+            raise ValueError("vis must be (N, K)")
+    lib = _lib.load()
+    steps = int(steps)
+    need = lib.hipe_keypoint_measures_workspace_bytes(K, steps)
+    ws = torch.empty((max(need, 8) // 8,), dtype=torch.float64, device=d.device)
+    summary = torch.empty((3,), dtype=torch.float64, device=d.device)
+    curve = torch.empty((max(steps, 0),), dtype=torch.float64, device=d.device)
+    with torch.cuda.device(d.device), _launch("keypoint_measures", d):
+        check(lib.hipe_keypoint_measures(d.data_ptr(), _ptr(v), N, K, float(val_min), float(val_max), steps,
+                                         summary.data_ptr(), curve.data_ptr(), ws.data_ptr(), ws.numel() * 8,
+                                         _stream(d)))
+    per = {"count": ws[0:K], "mean": ws[K:2 * K], "median": ws[2 * K:3 * K], "auc": ws[3 * K:4 * K],
+           "pck": ws[4 * K:4 * K + K * steps].view(K, steps)}
+    return {"summary": summary, "pck_curve": curve, "per_keypoint": per}
+
+
+def _f64(t, dev, shape=None):
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor):
+        import numpy as np
+        t = torch.as_tensor(np.ascontiguousarray(t, dtype=np.float64))
+    t = t.to(device=dev, dtype=torch.float64).contiguous()
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        raise ValueError("expected shape %s, got %s" % (tuple(shape), tuple(t.shape)))
+    return t
+
+
+def patch_to_camera(coords, N, J, tprime, K, trans=None, bbox=None, R=None, bone_len=None, bone=(9, 10),
+                    patch=(224.0, 224.0), dst=(224.0, 224.0), box_scale=1.0, gt=None, mode=0, optimal_scale=True,
+                    want=("cam",)):
+    """The coordinate chain of data/FreiHand/FreiHand.py:683-737 / :853-883 on the device, optionally
+    fused with the alignment against `gt` (hipe_eval_chain_procrustes).
+      coords : CUDA float32 (N, 3J) soft-argmax output, or float64 (N, J, 3|4) patch pixels
+      want   : any of "img", "cam" (chain only) or "cam", "Z", "pa_dist", "raw_dist" (with gt)
+    Returns a dict of CUDA fp64 tensors."""
+    _need_cuda(coords, "coords")
+    dev = coords.device
+    if coords.dtype == torch.float32 and coords.dim() == 2:
+        kind, stride = 0, 3
+        if tuple(coords.shape) != (N, 3 * J):
+            raise ValueError("soft-argmax coordinates must be (N, 3J)")
+        coords = coords.contiguous()
+    else:
+        coords = coords.to(torch.float64).contiguous()
+        if coords.dim() != 3 or coords.shape[0] != N or coords.shape[1] != J or coords.shape[2] < 3:
+            raise ValueError("patch coordinates must be (N, J, >=3)")
+        kind, stride = 1, int(coords.shape[2])
+    if trans is None and bbox is None:
+        raise ValueError("one of trans (N,3,3) or bbox (N,4) is required")
+    tprime, K = _f64(tprime, dev, (N,)), _f64(K, dev, (N, 3, 3))
+    trans, bbox = _f64(trans, dev, (N, 3, 3)), _f64(bbox, dev, (N, 4))
+    R, bone_len = _f64(R, dev, (N, 3, 3)), _f64(bone_len, dev, (N,))
+    shapes = {"img": (N, J, 3), "cam": (N, J, 3), "Z": (N, J, 3), "pa_dist": (N, J), "raw_dist": (N, J)}
+    out = {k: torch.empty(shapes[k], dtype=torch.float64, device=dev) for k in want}
+    lib = _lib.load()
+    common = (coords.data_ptr(), kind, stride, N, J, float(patch[0]), float(patch[1]), _ptr(trans), _ptr(bbox),
+              float(box_scale), float(dst[0]), float(dst[1]), tprime.data_ptr(), K.data_ptr(), _ptr(R),
+              _ptr(bone_len), int(bone[0]), int(bone[1]))
+    with torch.cuda.device(dev):
+        if gt is None:
+            if set(want) - {"img", "cam"}:
+                raise ValueError("Z / pa_dist / raw_dist need gt")
+            with _launch("patch_to_camera", coords):
+                check(lib.hipe_patch_to_camera(*common, _ptr(out.get("img")), _ptr(out.get("cam")), _stream(coords)))
+        else:
+            if "img" in want:
+                raise ValueError("img is only produced by the chain-only launch")
+            gt = _f64(gt, dev, (N, J, 3))
+            with _launch("eval_chain_procrustes", coords):
+                check(lib.hipe_eval_chain_procrustes(
+                    *common, gt.data_ptr(), int(mode), 1 if optimal_scale else 0, _ptr(out.get("cam")),
+                    _ptr(out.get("Z")), _ptr(out.get("pa_dist")), _ptr(out.get("raw_dist")), _stream(coords)))
     return out
 
 
@@ -345,3 +451,37 @@ class FusedJointLossFunction(torch.autograd.Function):
             check(_lib.load().hipe_scale_inplace(dlogits.data_ptr(), _logits_code(dlogits), dlogits.numel(),
                                                  gs.data_ptr(), _stream(dlogits)))
         return dlogits.view(ctx.in_shape), None, None, None, None, None, None, None
+
+
+class Orthonormalize3Function(torch.autograd.Function):
+    """make_orthonormal (procrustes_encoding/nrsfm/nrsfm_modules.py:46-67) for (..., 3, 3) CUDA
+    matrices, fp32 or fp64: U diag(1, 1, det(U V^T)) V^T with its exact derivative, one thread per
+    matrix (hipe_orthonormalize3_fwd / _bwd).  Saves 21 doubles per matrix."""
+
+    @staticmethod
+    def forward(ctx, mats):
+        _need_cuda(mats, "input_mat")
+        if mats.shape[-2:] != (3, 3):
+            raise ValueError("expected (..., 3, 3) matrices, got %s" % (tuple(mats.shape),))
+        if mats.dtype not in (torch.float32, torch.float64):
+            raise TypeError("orthonormalize3 takes float32 or float64 matrices")
+        a = mats.contiguous()
+        n = a.numel() // 9
+        code = _lib.F32 if a.dtype == torch.float32 else _lib.F64
+        out = torch.empty_like(a)
+        aux = torch.empty((n, 21), dtype=torch.float64, device=a.device)
+        with torch.cuda.device(a.device), _launch("orthonormalize3_fwd", a):
+            check(_lib.load().hipe_orthonormalize3_fwd(a.data_ptr(), code, n, out.data_ptr(), aux.data_ptr(), _stream(a)))
+        ctx.save_for_backward(aux)
+        ctx.code = code
+        return out
+
+    @staticmethod
+    def backward(ctx, grad):
+        (aux,) = ctx.saved_tensors
+        g = grad.contiguous()
+        n = g.numel() // 9
+        d = torch.empty_like(g)
+        with torch.cuda.device(g.device), _launch("orthonormalize3_bwd", g):
+            check(_lib.load().hipe_orthonormalize3_bwd(g.data_ptr(), ctx.code, n, aux.data_ptr(), d.data_ptr(), _stream(g)))
+        return d

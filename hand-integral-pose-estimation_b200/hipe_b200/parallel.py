@@ -86,6 +86,29 @@ def _local_cuda_loss(heatmap_out, gt_coord, gt_vis):
     return loss_sum, coords
 
 
+def _local_cuda_loss_fused(heatmap_out, gt_coord, gt_vis, norm):
+    """(norm * loss_sum_local [differentiable], coords) from ONE launch that also stores the heatmap
+    gradient already scaled by `norm` (ops.FusedJointLossFunction), so backward is a hand-over."""
+    from nets.loss import FreiHandConfig
+    from . import ops
+    joint_num = int(gt_coord.shape[1] / 3)
+    w, h = heatmap_out.shape[-1], heatmap_out.shape[-2]
+    d = heatmap_out.shape[-3] // FreiHandConfig.num_joints
+    scaled, coords = ops.FusedJointLossFunction.apply(heatmap_out, gt_coord.to(torch.float64),
+                                                      gt_vis.to(torch.float64), joint_num, d, h, w, norm)
+    return scaled, coords
+
+
+def _fused_plan(heatmap_out, gt_coord):
+    from nets.loss import FreiHandConfig
+    from . import ops
+    if not (heatmap_out.is_cuda and torch.is_grad_enabled() and heatmap_out.requires_grad):
+        return None
+    d = heatmap_out.shape[-3] // FreiHandConfig.num_joints
+    n_vol = heatmap_out.shape[0] * int(gt_coord.shape[1] / 3)
+    return ops.fused_plan(heatmap_out, n_vol, d, heatmap_out.shape[-2], heatmap_out.shape[-1])
+
+
 class ShardedJointLocationLoss(nn.Module):
     """JointLocationLoss over a batch sharded across the ranks of `group`.
 
@@ -110,15 +133,27 @@ class ShardedJointLocationLoss(nn.Module):
 
     def forward(self, heatmap_out, gt_coord, gt_vis):
         world = dist.get_world_size(self.group)
-        loss_sum, coords = self.local_fn(heatmap_out, gt_coord, gt_vis)
-        b_local, k = coords.shape
         counts = None
+        scaled = None
         if self.global_batch is not None:
             counts = [hi - lo for lo, hi in (shard_bounds(self.global_batch, world, r) for r in range(world))]
+            b_local = heatmap_out.shape[0]
             if counts[dist.get_rank(self.group)] != b_local:
                 raise ValueError("this rank holds %d rows, shard_bounds(%d, %d) gives it %d"
                                  % (b_local, self.global_batch, world, counts[dist.get_rank(self.group)]))
             b_max = max_shard(self.global_batch, world)
+            if self.local_fn is _local_cuda_loss and b_local > 0 and _fused_plan(heatmap_out, gt_coord):
+                # shard sizes known a priori => so is this replica's weight in the global loss: the
+                # single-launch kernel can store the finished gradient (no scaling pass in backward)
+                live = sum(1 for c in counts if c > 0)
+                norm = 1.0 / (b_local * live) if self.size_average else 1.0 / live
+                scaled, coords = _local_cuda_loss_fused(heatmap_out, gt_coord, gt_vis, norm)
+                loss_sum = scaled.detach() / norm
+        if scaled is None:
+            loss_sum, coords = self.local_fn(heatmap_out, gt_coord, gt_vis)
+        b_local, k = coords.shape
+        if self.global_batch is not None:
+            pass
         else:
             # one extra tiny collective only when the caller did not promise the shard sizes
             t = torch.tensor([b_local], dtype=torch.int64, device=coords.device)
@@ -131,6 +166,8 @@ class ShardedJointLocationLoss(nn.Module):
         self.coords = allc.to(coords.dtype)
         if b_local == 0:
             return value
+        if scaled is not None:
+            return value + (scaled - scaled.detach())
         # value of the global loss, gradient of this replica's share (1/live of its own loss)
         own = loss_sum / b_local if self.size_average else loss_sum
         return value + (own - own.detach()) / live

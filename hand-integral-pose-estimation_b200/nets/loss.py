@@ -48,10 +48,13 @@ def softmax_integral_tensor2(preds, num_joints, hm_width, hm_height, hm_depth):
 
 
 class JointLocationLoss(nn.Module):
-    """loss.py:69-91.  `fused=True` computes the heatmap gradient in the forward launch
-    (one read + one write of the volume from HBM instead of two reads + one write)."""
+    """loss.py:69-91.  When the heatmaps require a gradient the loss and `dlogits` can come out
+    of ONE launch (one read + one write of each volume from HBM instead of two reads + one
+    write); backward then only hands the stored gradient over.  `fused=None` (default) takes
+    that path for the geometries where it is measured faster (ops.fused_plan), `True` / `False`
+    force / forbid it."""
 
-    def __init__(self, fused=False):
+    def __init__(self, fused=None):
         super(JointLocationLoss, self).__init__()
         self.size_average = True
         self.fused = fused
@@ -63,7 +66,10 @@ class JointLocationLoss(nn.Module):
         hm_depth = heatmap_out.shape[-3] // FreiHandConfig.num_joints
         B = heatmap_out.shape[0]
         norm = 1.0 / B if self.size_average else 1.0
-        if self.fused and torch.is_grad_enabled() and heatmap_out.requires_grad:
+        fused = self.fused
+        if fused is None and torch.is_grad_enabled() and heatmap_out.requires_grad and heatmap_out.is_cuda:
+            fused = ops.fused_plan(heatmap_out, B * joint_num, hm_depth, hm_height, hm_width) is not None
+        if fused and torch.is_grad_enabled() and heatmap_out.requires_grad:
             loss, _ = ops.FusedJointLossFunction.apply(heatmap_out, gt_coord, gt_vis, joint_num, hm_depth,
                                                        hm_height, hm_width, norm)
             return loss

@@ -169,6 +169,71 @@ HIPE_API int hipe_procrustes_batched(const double* X_dev, const double* Y_dev, l
                             double* raw_dist_dev, void* stream);
 
 /*
+ * Patch -> camera coordinate chain that sits between the soft-argmax and the alignment in the
+ * reference's evaluators (data/FreiHand/FreiHand.py:683-737 and :853-883), per joint in fp64:
+ *   get_joint_location_result rescale (common/augment.py:176-178; coords_kind 0 only),
+ *   trans_coords_from_patch_to_org_3d (common/augment.py:186-217,508-511),
+ *   pixel2cam (common/augment.py:89-103), R^T (FreiHand.py:722; R_dev nullable),
+ *   scale_result(method='scale') on the bone joint_a-joint_b (FreiHand.py:632-653; bone_len_dev nullable).
+ *   coords_dev   : coords_kind 0: N*3J floats, the soft-argmax output (x, y, z in [-0.5, 0.5));
+ *                  coords_kind 1: N*J*coords_stride doubles, patch pixels (stride 4 = with score)
+ *   trans_dev    : N*9 row-major patch->image matrices (gts[n]['trans']), or NULL to build
+ *                  gen_trans_from_patch_cv(cx, cy, w, h, dst_w, dst_h, box_scale, inv=True)
+ *                  (common/augment.py:457-506) from bbox_dev N*4 = (cx, cy, w, h)
+ *   tprime_dev N, K_dev N*9, R_dev N*9, bone_len_dev N   (all fp64)
+ *   img_dev N*J*3 : image-space (u, v, z_mm) (nullable);  cam_dev N*J*3 : camera space, metres (nullable)
+ * J <= 512.
+ */
+HIPE_API int hipe_patch_to_camera(const void* coords_dev, int coords_kind, int coords_stride, long long N, int J,
+                         double patch_w, double patch_h, const double* trans_dev, const double* bbox_dev,
+                         double box_scale, double dst_w, double dst_h, const double* tprime_dev,
+                         const double* K_dev, const double* R_dev, const double* bone_len_dev, int joint_a,
+                         int joint_b, double* img_dev, double* cam_dev, void* stream);
+
+/*
+ * The same chain fused in front of hipe_procrustes_batched (one launch, the camera-space joints
+ * stay in shared memory): the per-sample body of FreiHand.evaluate (FreiHand.py:703-767).
+ *   X_dev N*J*3 : ground-truth joints (gt_3d_kpt);  cam_dev, Z_dev, pa_dist_dev, raw_dist_dev nullable.
+ */
+HIPE_API int hipe_eval_chain_procrustes(const void* coords_dev, int coords_kind, int coords_stride, long long N,
+                               int J, double patch_w, double patch_h, const double* trans_dev,
+                               const double* bbox_dev, double box_scale, double dst_w, double dst_h,
+                               const double* tprime_dev, const double* K_dev, const double* R_dev,
+                               const double* bone_len_dev, int joint_a, int joint_b, const double* X_dev,
+                               int mode, int optimal_scale, double* cam_dev, double* Z_dev,
+                               double* pa_dist_dev, double* raw_dist_dev, void* stream);
+
+/*
+ * FreiHAND keypoint measures: replaces EvalUtil.feed + EvalUtil.get_measures (main/eval.py:25-106)
+ * on per-sample per-keypoint distances that are already on the device (pa_dist / raw_dist above).
+ *   dist_dev      : N*K doubles, ||gt - pred||_2 per keypoint (main/eval.py:40-41)
+ *   vis_dev       : N*K bytes, non-zero = the keypoint was visible and is fed (nullable = all)
+ *   thresholds    : np.linspace(val_min, val_max, steps) (main/eval.py:65); steps <= 1024
+ *   summary_dev   : 3 doubles: mean EPE, median EPE, AUC, each the mean over fed keypoints
+ *   pck_curve_dev : `steps` doubles, PCK per threshold averaged over fed keypoints
+ *   workspace_dev : hipe_keypoint_measures_workspace_bytes(K, steps) bytes of caller-owned scratch;
+ *                   afterwards it holds, per keypoint, [count K][mean K][median K][auc K][pck K*steps]
+ */
+HIPE_API long long hipe_keypoint_measures_workspace_bytes(int K, int steps);
+HIPE_API int hipe_keypoint_measures(const double* dist_dev, const unsigned char* vis_dev, long long N, int K,
+                           double val_min, double val_max, int steps, double* summary_dev,
+                           double* pck_curve_dev, double* workspace_dev, long long workspace_bytes,
+                           void* stream);
+
+/*
+ * Batched 3x3 orthonormalisation: replaces make_orthonormal
+ * (procrustes_encoding/nrsfm/nrsfm_modules.py:46-67) and the SVD it takes from the external
+ * torch_batch_svd extension (procrustes_encoding/nrsfm/batch_svd.py:5-35).
+ *   A_dev N*9 (row-major 3x3) of `dtype` (HIPE_F32 | HIPE_F64) -> R_dev N*9 = U diag(1,1,det(UV^T)) V^T
+ *   aux_dev N*21 doubles (U, V, signed singular values): input of the backward (nullable)
+ *   backward: G_dev = dL/dR -> dA_dev = dL/dA
+ */
+HIPE_API int hipe_orthonormalize3_fwd(const void* A_dev, int dtype, long long N, void* R_dev, double* aux_dev,
+                             void* stream);
+HIPE_API int hipe_orthonormalize3_bwd(const void* G_dev, int dtype, long long N, const double* aux_dev,
+                             void* dA_dev, void* stream);
+
+/*
  * Host-buffer convenience entry points (synchronous).
  * hipe_joint_location_loss_host: JointLocationLoss forward (+ backward when dlogits_host or
  * dlogits_dev is non-NULL) on host logits, streamed to the current device in chunks of

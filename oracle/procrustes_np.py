@@ -99,3 +99,24 @@ def keypoint_measures(gt, pred, val_min=0.0, val_max=0.05, steps=100):
     pck = (dist[:, :, None] <= thr[None, None, :]).mean(axis=0)      # (K, steps)
     auc = np.trapezoid(pck, thr, axis=1) / span
     return dist.mean(axis=0).mean(), np.median(dist, axis=0).mean(), auc.mean(), pck.mean(axis=0), thr
+
+
+def keypoint_measures_masked(dist, vis, val_min=0.0, val_max=0.05, steps=100):
+    """main/eval.py:25-106 with the visibility gate of `feed` (:45-47): keypoint k only collects the
+    distances of samples with vis[n, k] true; keypoints that collected nothing are skipped in
+    the final means (:76-78).  dist, vis: (N, K)."""
+    dist = np.asarray(dist, np.float64)
+    vis = np.asarray(vis).astype(bool)
+    thr = np.linspace(val_min, val_max, steps)
+    span = np.trapezoid(np.ones_like(thr), thr)
+    means, medians, aucs, curves = [], [], [], []
+    for k in range(dist.shape[1]):
+        d = dist[vis[:, k], k]
+        if d.size == 0:
+            continue
+        means.append(d.mean())
+        medians.append(np.median(d))
+        pck = np.array([np.mean((d <= t).astype(float)) for t in thr])
+        curves.append(pck)
+        aucs.append(np.trapezoid(pck, thr) / span)
+    return np.mean(means), np.mean(medians), np.mean(aucs), np.mean(np.array(curves), 0), thr

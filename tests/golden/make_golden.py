@@ -186,6 +186,19 @@ def chain_case():
     return out
 
 
+def orthonormal_case():
+    """make_orthonormal (nrsfm_modules.py:46-67) forward and its autograd backward in fp64 on
+    random, reflected, nearly singular and nearly rotation matrices."""
+    M = ref_loader.load_nrsfm_modules()
+    A = synth.matrices3(96, seed=401)
+    G = np.random.default_rng(402).standard_normal(A.shape)
+    a = torch.as_tensor(A).clone().requires_grad_(True)
+    r = M.make_orthonormal(a)
+    (r * torch.as_tensor(G)).sum().backward()
+    return {"A": A, "G": G, "R": r.detach().numpy(), "dA": a.grad.numpy(),
+            "det": M.batch_det_3x3(torch.as_tensor(A)).numpy()}
+
+
 def main():
     if not ref_loader.available():
         raise SystemExit("the reference tree is not mounted; goldens can only be made in the build container")
@@ -198,6 +211,9 @@ def main():
     ch = chain_case()
     np.savez_compressed(os.path.join(HERE, "chain.npz"), **ch)
     print("chain PA-MPJPE %.6f m, MPJPE %.6f m" % (ch["pa_mpjpe"], ch["mpjpe"]))
+    o = orthonormal_case()
+    np.savez_compressed(os.path.join(HERE, "orthonormal.npz"), **o)
+    print("orthonormal: max |R^T R - I| %.2e" % np.abs(np.einsum("nji,njk->nik", o["R"], o["R"]) - np.eye(3)).max())
     if "--chain-only" in sys.argv:
         return
     p = procrustes_cases()

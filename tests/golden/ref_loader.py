@@ -118,6 +118,33 @@ def load_chain_functions():
     return _cache["chain"]
 
 
+def load_nrsfm_modules():
+    """The unmodified procrustes_encoding/nrsfm/nrsfm_modules.py (make_orthonormal :46-67,
+    batch_det_3x3 :24-43).  Its `from .batch_svd import batch_svd` needs the external
+    torch_batch_svd CUDA extension (absent): a stand-in package provides
+    `batch_svd(x) -> (U, S, V)` with x = U S V^T, descending S -- that extension's contract --
+    from torch.linalg.svd."""
+    if "nrsfm" not in _cache:
+        import torch
+        pkg = types.ModuleType("_hipe_ref_nrsfm")
+        pkg.__path__ = []
+        sub = types.ModuleType("_hipe_ref_nrsfm.batch_svd")
+
+        def batch_svd(x):
+            u, s, vh = torch.linalg.svd(x)
+            return u, s, vh.transpose(1, 2)
+
+        sub.batch_svd = batch_svd
+        sys.modules["_hipe_ref_nrsfm"] = pkg
+        sys.modules["_hipe_ref_nrsfm.batch_svd"] = sub
+        spec = importlib.util.spec_from_file_location(
+            "_hipe_ref_nrsfm.nrsfm_modules", os.path.join(REF, "procrustes_encoding", "nrsfm", "nrsfm_modules.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        _cache["nrsfm"] = mod
+    return _cache["nrsfm"]
+
+
 def fixture_arrays():
     """The two joint-set arrays the reference ships."""
     import numpy as np

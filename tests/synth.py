@@ -89,3 +89,16 @@ def chain_inputs(n, J=21, seed=0, patch=224.0):
     pt[..., 0:3] += rng.standard_normal((n, J, 3)) * np.array([2.0, 2.0, 4.0])
     bone = np.sqrt(((gt_cam[:, 9] - gt_cam[:, 10]) ** 2).sum(axis=1))
     return {"patch": pt, "bbox": bbox, "tprime": tprime, "K": K, "R": R, "bone_len": bone, "gt_cam": gt_cam}
+
+
+def matrices3(n, seed=0):
+    """3x3 matrices for the orthonormalisation: generic, with negative determinant (the flip must
+    act), one small singular value, and near-rotations (the PANet camera's usual input)."""
+    rng = np.random.default_rng(seed)
+    A = rng.standard_normal((n, 3, 3))
+    A[1::4] = random_rotations(len(A[1::4]), rng) + rng.standard_normal(A[1::4].shape) * 0.05
+    A[2::4, :, 0] *= -1.0
+    q = random_rotations(len(A[3::4]), rng)
+    sv = np.stack([rng.uniform(1, 2, len(q)), rng.uniform(0.3, 0.9, len(q)), rng.uniform(0.02, 0.1, len(q))], axis=1)
+    A[3::4] = np.einsum("nij,nj,nkj->nik", q, sv, random_rotations(len(q), rng))
+    return A

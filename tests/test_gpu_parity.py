@@ -111,7 +111,7 @@ def test_backward_grads_when_E_sits_on_the_peak(geom, case):
                 "geom %s %s cluster %d variant %d: %.3e" % (geom, case, cluster, variant, rel.max())
 
 
-@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("fused", [False, True, None])
 @pytest.mark.parametrize("tgt", [np.float64, np.float32])
 @pytest.mark.parametrize("geom", [(16, 16, 16), (64, 64, 64), (5, 6, 7)])
 def test_joint_location_loss_module(fused, tgt, geom):

@@ -151,6 +151,8 @@ def test_module_uses_resident_launch_and_scales_upstream_gradient():
     hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=9)
     gt, vis = synth.targets(B, J, seed=9)
     ops.KERNEL_EVENTS = {}
+    saved = ops.FUSED_MODE
+    ops.FUSED_MODE = "resident"          # 32^3 is not a geometry fused_plan gives to this launch
     try:
         x = _cuda(hm).requires_grad_(True)
         loss = L.JointLocationLoss(fused=True)(x, _cuda(gt), _cuda(vis))
@@ -158,7 +160,39 @@ def test_module_uses_resident_launch_and_scales_upstream_gradient():
         assert "joint_loss_resident" in ops.KERNEL_EVENTS
     finally:
         ops.KERNEL_EVENTS = None
+        ops.FUSED_MODE = saved
     y = _cuda(hm).requires_grad_(True)
     L.JointLocationLoss()(y, _cuda(gt), _cuda(vis)).backward()
     scale = y.grad.view(B * J, -1).abs().amax(dim=1, keepdim=True)
     assert ((x.grad - 0.25 * y.grad).view(B * J, -1).abs() <= 2e-5 * 0.25 * scale + 1e-12).all()
+
+
+def test_default_module_picks_the_measured_fastest_launch():
+    """fused=None: 21x64^3 fp32 batches go to the resident launch, other fp32 volumes >= 512 KB to
+    the streaming fused launch, bf16 and small volumes to forward + recompute backward."""
+    from hipe_b200 import ops
+    from nets import loss as L
+    x64 = torch.empty((16, 21 * 64, 64, 64), device="cuda")
+    assert ops.fused_plan(x64, 16 * 21, 64, 64, 64) == "resident"
+    assert ops.fused_plan(x64[:2], 42, 64, 64, 64) == "stream"           # too few volumes to fill the grid
+    assert ops.fused_plan(x64.bfloat16(), 16 * 21, 64, 64, 64) is None
+    x56 = torch.empty((2, 21 * 56, 56, 56), device="cuda")
+    assert ops.fused_plan(x56, 42, 56, 56, 56) == "stream"
+    x16 = torch.empty((2, 21 * 16, 16, 16), device="cuda")
+    assert ops.fused_plan(x16, 42, 16, 16, 16) is None
+    hm = synth.heatmaps(16, 21, 64, 64, 64, "peaked", seed=11)
+    gt, vis = synth.targets(16, 21, seed=11)
+    ops.KERNEL_EVENTS = {}
+    try:
+        x = _cuda(hm).requires_grad_(True)
+        loss = L.JointLocationLoss()(x, _cuda(gt), _cuda(vis))
+        loss.backward()
+        assert "joint_loss_resident" in ops.KERNEL_EVENTS and "softargmax_bwd" not in ops.KERNEL_EVENTS
+    finally:
+        ops.KERNEL_EVENTS = None
+    y = _cuda(hm).requires_grad_(True)
+    l2 = L.JointLocationLoss(fused=False)(y, _cuda(gt), _cuda(vis))
+    l2.backward()
+    assert abs(loss.item() - l2.item()) <= 1e-9 * abs(l2.item())
+    scale = y.grad.view(16 * 21, -1).abs().amax(dim=1, keepdim=True)
+    assert ((x.grad - y.grad).view(16 * 21, -1).abs() <= 2e-5 * scale + 1e-12).all()
