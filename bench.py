@@ -3,16 +3,19 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-A step = one pass of the path over one batch: JointLocationLoss forward (soft-argmax kernel +
-fp64 L1 kernel) and backward (recompute kernel) on `--batch` samples of 21 x 64^3 fp32 logits
-(BASELINE.json configs[1]) per GPU.  Prints ONE JSON line (rank 0):
+A step = one pass of the path over one batch: `loss = JointLocationLoss()(heatmaps, gt, vis);
+loss.backward()` through the drop-in module on `--batch` samples of 21 x 64^3 fp32 logits
+(BASELINE.json configs[1]) per GPU.  The module picks the launch plan itself (ops.fused_plan):
+at this geometry ONE persistent launch that reads every volume once and writes its gradient once
+(hipe_joint_loss_resident); the forward + recompute-backward pair is timed in the same run and
+reported under `other_plan`.  Prints ONE JSON line (rank 0):
 
   value      volumes/s, whole job, inputs resident in HBM, CUDA events, max over ranks
   e2e        the same metric through the C-ABI host entry point hipe_joint_location_loss_host:
              pinned HOST logits/targets in, loss + joints back to the host, the gradient left in
              a device buffer where the head's backward would consume it
-  roofline   the dominant kernel (backward: reads V, writes V per volume), timed live with CUDA
-             events on the launching stream inside the timed region
+  roofline   the dominant kernel (single launch or backward: reads V, writes V per volume), timed
+             live with CUDA events on the launching stream inside the timed region
   cpu_baseline  the reference's PyTorch-eager op sequence (oracle/integral_torch.py, a port:
              /root/reference does not travel) on this box's host cores, bounded sample
   --impl reference  times that CPU port alone on the same workload definition.
@@ -44,7 +47,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=64, help="samples per GPU (weak scaling)")
     ap.add_argument("--dim", type=int, default=64)
     ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"])
-    ap.add_argument("--fused", action="store_true", help="time the single-launch fused loss+grad kernel instead")
+    ap.add_argument("--fused", action="store_true", help="force the single-launch loss+grad path as the primary arm")
+    ap.add_argument("--two-launch", action="store_true", help="force forward + recompute backward as the primary arm")
+    ap.add_argument("--no-alt", action="store_true", help="skip timing the other launch plan for comparison")
     ap.add_argument("--e2e-steps", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -54,7 +59,7 @@ def parse():
 
 
 def workload_name(a):
-    return "JointLocationLoss fwd+bwd (soft-argmax + L1 + recompute backward), %s logits, batch %d/GPU, 21x%d^3" % (
+    return "JointLocationLoss fwd+bwd (soft-argmax + L1 integral loss + heatmap gradient), %s logits, batch %d/GPU, 21x%d^3" % (
         "fp32" if a.dtype == "f32" else "bf16", a.batch, a.dim)
 
 
@@ -209,17 +214,15 @@ def run_ours(a):
     g = torch.Generator(device=dev).manual_seed(99 + rank)
     gt = torch.rand(B, 3 * J, generator=g, device=dev, dtype=torch.float64) - 0.5
     vis = torch.ones_like(gt)
-    if world > 1:
-        crit = parallel.ShardedJointLocationLoss(global_batch=B * world)
-    else:
-        crit = L.JointLocationLoss(fused=a.fused)
+    fused_flag = True if a.fused else (False if a.two_launch else None)     # None = the library's own choice
 
-    def step(i):
-        x = xs[i % NBUF]
-        x.grad = None
-        loss = crit(x, gt, vis)
-        loss.backward()
-        return loss
+    def make_crit(fused):
+        if world > 1:
+            c = parallel.ShardedJointLocationLoss(global_batch=B * world)
+            if fused is False:
+                c.local_fn = lambda h, g_, v_: parallel._local_cuda_loss(h, g_, v_)   # never the fused launch
+            return c
+        return L.JointLocationLoss(fused=fused)
 
     def barrier():
         torch.cuda.synchronize()
@@ -227,30 +230,59 @@ def run_ours(a):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(max(a.warmup, 3)):
-        step(i)
-    barrier()
-    sampler = ClockSampler(local)
-    sampler.start()
-    ops.KERNEL_EVENTS = {}
-    launches0 = ops.LAUNCHES
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(a.steps):
-        last = step(i)
-    e1.record()
-    barrier()
-    sampler.stop_flag.set()
-    ms = e0.elapsed_time(e1)
-    launches = ops.LAUNCHES - launches0
-    events, ops.KERNEL_EVENTS = ops.KERNEL_EVENTS, None
-    kern = {k: sum(s.elapsed_time(e) for s, e in v) / len(v) for k, v in events.items()}
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    loss_value = float(last.item())
+    host_ms = [0.0]
+
+    def timed(crit, steps, warm, sample_clocks):
+        """W untimed + K timed steps of crit; CUDA events, barrier on both sides, max over ranks."""
+        def step(i):
+            x = xs[i % NBUF]
+            x.grad = None
+            loss = crit(x, gt, vis)
+            loss.backward()
+            return loss
+        for i in range(warm):
+            step(i)
+        barrier()
+        sampler = ClockSampler(local) if sample_clocks else None
+        if sampler:
+            sampler.start()
+        events = {}
+        launches0 = ops.LAUNCHES
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        h0 = time.perf_counter()
+        for i in range(steps):
+            # per-kernel event pairs on every 4th step only: they cost host time, and at ~0.5 ms of
+            # kernels per step the enqueue rate matters
+            ops.KERNEL_EVENTS = events if i % 4 == 0 else None
+            last = step(i)
+        ops.KERNEL_EVENTS = None
+        host_ms[0] = 1e3 * (time.perf_counter() - h0) / steps      # host time to ENQUEUE one step
+        e1.record()
+        barrier()
+        if sampler:
+            sampler.stop_flag.set()
+        ms_ = e0.elapsed_time(e1)
+        n_launch = ops.LAUNCHES - launches0
+        kern_ = {k: sum(s_.elapsed_time(e_) for s_, e_ in v) / len(v) for k, v in events.items()}
+        t_ = torch.tensor([ms_], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+        return float(t_.item()), kern_, n_launch, float(last.item()), sampler
+
+    crit = make_crit(fused_flag)
+    ms, kern, launches, loss_value, sampler = timed(crit, a.steps, max(a.warmup, 3), True)
     value = world * n_vol * a.steps / (ms / 1e3)
+    host_enqueue_ms = host_ms[0]
+    single_launch = ("joint_loss_resident" in kern) or ("joint_loss_fused" in kern)
+    # the other launch plan, same buffers, same K: reported beside the primary, never as `value`
+    alt = None
+    if not a.no_alt and not (a.fused or a.two_launch) and (world == 1 or single_launch):
+        ms2, kern2, _, loss2, _ = timed(make_crit(not single_launch), a.steps, max(a.warmup, 3), False)
+        alt = {"plan": "two launches (forward + recompute backward)" if single_launch else "single launch (loss + gradient)",
+               "value": world * n_vol * a.steps / (ms2 / 1e3), "unit": UNIT, "ms_per_step": ms2 / a.steps,
+               "kernels_ms": kern2, "loss": loss2,
+               "step_hbm_GBs": n_vol * ((3 if single_launch else 2) * V * esz) / (ms2 / a.steps) / 1e6}
 
     # ---- roofline of the dominant kernel ----
     peak, peak_src = FALLBACK_HBM_GBS, "fallback"
@@ -262,10 +294,10 @@ def run_ours(a):
     traffic = None
     try:
         prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic = prof.get(("resident" if "joint_loss_resident" in kern else "fused") if a.fused else "softargmax_bwd", {}).get("%s_%d_B%d" % (a.dtype, D, B))
+        traffic = prof.get(("resident" if "joint_loss_resident" in kern else "fused") if single_launch else "softargmax_bwd", {}).get("%s_%d_B%d" % (a.dtype, D, B))
     except Exception:
         pass
-    if a.fused:
+    if single_launch:
         dom = "joint_loss_resident" if "joint_loss_resident" in kern else "joint_loss_fused"
         per_vol = 2 * V * esz                                    # one HBM read + one write per volume
     else:
@@ -276,7 +308,7 @@ def run_ours(a):
                 "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": n_vol * per_vol,
                 "launch_ms": dom_ms}
-    step_bytes = n_vol * ((2 if a.fused else 3) * V * esz)
+    step_bytes = n_vol * ((2 if single_launch else 3) * V * esz)
     kernels = {k: {"ms": v} for k, v in kern.items()}
     if "softargmax_fwd" in kern:
         kernels["softargmax_fwd"]["GBs"] = n_vol * V * esz / kern["softargmax_fwd"] / 1e6
@@ -341,11 +373,13 @@ def run_ours(a):
                        "volume": [D, D, D], "parallelism": "batch-sharded x%d, one packed all-gather per step" % world
                        if world > 1 else "single GPU",
                        "l2": "inputs larger than L2: %d rotating %.2f GB logit buffers per GPU" % (NBUF, n_vol * V * esz / 1e9),
-                       "regime": "peaked (A=12, sigma=2) + N(0,1)", "fused_single_launch": bool(a.fused)},
+                       "regime": "peaked (A=12, sigma=2) + N(0,1)", "launch_plan": ("single launch: loss + gradient, one HBM read + one write per volume (%s)" % dom)
+                       if single_launch else "two launches: forward (read V) + recompute backward (read V, write V)",
+                       "algorithmic_bytes_per_volume": (2 if single_launch else 3) * V * esz},
             "step_hbm_GBs": step_bytes / (ms / a.steps) / 1e6,
             "step_frac_of_peak": step_bytes / (ms / a.steps) / 1e6 / peak,
-            "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
-            "gpu_launches": launches, "clocks": sampler.summary(), "loss": loss_value}
+            "roofline": roofline, "kernels": kernels, "other_plan": alt, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": launches, "host_enqueue_ms_per_step": host_enqueue_ms, "clocks": sampler.summary(), "loss": loss_value}
     print(json.dumps(line), flush=True)
 
 

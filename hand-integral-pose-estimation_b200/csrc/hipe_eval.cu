@@ -53,11 +53,11 @@ __global__ void __launch_bounds__(kRedThreads)
 
 // x *= *gscale, skipped entirely (no memory traffic) when the scalar is exactly 1: lets the
 // fused loss hand back the gradient it computed in the forward launch without a host sync.
-template <typename T>
+template <typename T, typename S>
 __global__ void __launch_bounds__(256) k_scale_inplace(unsigned char* __restrict__ x, long long n_vec,
                                                          long long n_tail_start, long long n,
-                                                         const float* __restrict__ gscale) {
-    const float g = *gscale;
+                                                         const S* __restrict__ gscale) {
+    const float g = (float)*gscale;
     if (g == 1.0f) return;
     using V16 = Vec16<T>;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec;
@@ -634,7 +634,8 @@ extern "C" int hipe_sum_f64(const double* in, long long n, double scale, double*
     return (int)cudaGetLastError();
 }
 
-extern "C" int hipe_scale_inplace(void* x, int dtype, long long n, const float* gscale, void* stream) {
+template <typename S>
+static int scale_inplace_impl(void* x, int dtype, long long n, const S* gscale, void* stream) {
     if (!x || !gscale) return HIPE_E_NULL;
     if (n < 0) return HIPE_E_SHAPE;
     if (dtype != HIPE_F32 && dtype != HIPE_BF16) return HIPE_E_DTYPE;
@@ -647,10 +648,21 @@ extern "C" int hipe_scale_inplace(void* x, int dtype, long long n, const float* 
     if (grid > 148 * 8) grid = 148 * 8;
     if (grid < 1) grid = 1;
     if (dtype == HIPE_F32)
-        k_scale_inplace<float><<<(unsigned)grid, 256, 0, st>>>(static_cast<unsigned char*>(x), n_vec, n_vec * per, n, gscale);
+        k_scale_inplace<float, S><<<(unsigned)grid, 256, 0, st>>>(static_cast<unsigned char*>(x), n_vec, n_vec * per, n, gscale);
     else
-        k_scale_inplace<__nv_bfloat16><<<(unsigned)grid, 256, 0, st>>>(static_cast<unsigned char*>(x), n_vec, n_vec * per, n, gscale);
+        k_scale_inplace<__nv_bfloat16, S><<<(unsigned)grid, 256, 0, st>>>(static_cast<unsigned char*>(x), n_vec, n_vec * per, n, gscale);
     return (int)cudaGetLastError();
+}
+
+extern "C" int hipe_scale_inplace(void* x, int dtype, long long n, const float* gscale, void* stream) {
+    return scale_inplace_impl<float>(x, dtype, n, gscale, stream);
+}
+
+extern "C" int hipe_scale_inplace_s(void* x, int dtype, long long n, const void* gscale, int gscale_dtype,
+                                    void* stream) {
+    if (gscale_dtype == HIPE_F32) return scale_inplace_impl<float>(x, dtype, n, static_cast<const float*>(gscale), stream);
+    if (gscale_dtype == HIPE_F64) return scale_inplace_impl<double>(x, dtype, n, static_cast<const double*>(gscale), stream);
+    return HIPE_E_DTYPE;
 }
 
 extern "C" int hipe_procrustes_batched(const double* X, const double* Y, long long N, int J, int mode,

@@ -29,6 +29,7 @@ SIGNATURES = {
     "hipe_joint_loss_resident": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp,
                                       _vp, _ll, _vp]),
     "hipe_scale_inplace": (_i, [_vp, _i, _ll, _vp, _vp]),
+    "hipe_scale_inplace_s": (_i, [_vp, _i, _ll, _vp, _i, _vp]),
     "hipe_sum_f64": (_i, [_vp, _ll, _d, _vp, _vp]),
     "hipe_procrustes_batched": (_i, [_vp, _vp, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hipe_patch_to_camera": (_i, [_vp, _i, _i, _ll, _i, _d, _d, _vp, _vp, _d, _d, _d, _vp, _vp, _vp, _vp, _i, _i,

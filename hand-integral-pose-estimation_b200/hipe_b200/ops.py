@@ -45,6 +45,23 @@ class _launch:
         return False
 
 
+class _on:
+    """`with _on(dev)` only when dev is not already current (the context manager costs
+    ~10 us of host time per launch, a tenth of the step's launch budget)."""
+
+    def __init__(self, dev):
+        self.ctx = None if dev.index == torch.cuda.current_device() else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            return self.ctx.__exit__(*exc)
+        return False
+
+
 def _need_cuda(t, name):
     if not isinstance(t, torch.Tensor):
         raise TypeError("%s must be a torch.Tensor, got %s" % (name, type(t).__name__))
@@ -80,7 +97,7 @@ def softargmax_forward(logits, n_vol, D, H, W, apply_softmax=True, cluster=None,
     coords = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
     expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev)
     stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev), _launch("softargmax_fwd", logits):
+    with _on(dev), _launch("softargmax_fwd", logits):
         check(_lib.load().hipe_softargmax_fwd(
             logits.data_ptr(), code, n_vol, D, H, W, 1 if apply_softmax else 0,
             coords.data_ptr(), expect.data_ptr(), stats.data_ptr(),
@@ -101,7 +118,7 @@ def softargmax_backward(logits, n_vol, D, H, W, stats, expect, gcoords, gscale=N
     if gscale is not None:
         gscale = gscale.to(device=logits.device, dtype=torch.float32).reshape(1).contiguous()
     out = torch.empty_like(logits)
-    with torch.cuda.device(logits.device), _launch("softargmax_bwd", logits):
+    with _on(logits.device), _launch("softargmax_bwd", logits):
         check(_lib.load().hipe_softargmax_bwd(
             logits.data_ptr(), code, n_vol, D, H, W, stats.data_ptr(), expect.data_ptr(),
             gcoords.data_ptr(), _ptr(gscale), out.data_ptr(),
@@ -119,7 +136,7 @@ def volume_softmax(logits, n_vol, D, H, W, stats=None, cluster=None, variant=Non
     if stats is None:
         _, _, stats = softargmax_forward(logits, n_vol, D, H, W, True, cluster, variant)
     out = torch.empty_like(logits)
-    with torch.cuda.device(logits.device), _launch("volume_softmax", logits):
+    with _on(logits.device), _launch("volume_softmax", logits):
         check(_lib.load().hipe_volume_softmax(
             logits.data_ptr(), code, n_vol, D, H, W, stats.data_ptr(), out.data_ptr(),
             DEFAULT_CLUSTER if cluster is None else cluster,
@@ -147,7 +164,7 @@ def l1_loss(coords, gt, vis, norm, want_grad=True):
     B, K = coords.shape
     loss = torch.empty((), dtype=torch.float64, device=coords.device)
     g = torch.empty_like(coords) if want_grad else None
-    with torch.cuda.device(coords.device), _launch("l1_loss", coords):
+    with _on(coords.device), _launch("l1_loss", coords):
         check(_lib.load().hipe_l1_loss_fwd(coords.data_ptr(), gt.data_ptr(), vis.data_ptr(), code, B, K,
                                            float(norm), loss.data_ptr(), _ptr(g), _stream(coords)))
     return loss, g
@@ -157,7 +174,7 @@ def sum_f64(x, scale=1.0):
     _need_cuda(x, "x")
     x = x.to(torch.float64).contiguous()
     out = torch.empty((), dtype=torch.float64, device=x.device)
-    with torch.cuda.device(x.device), _launch("sum_f64", x):
+    with _on(x.device), _launch("sum_f64", x):
         check(_lib.load().hipe_sum_f64(x.data_ptr(), x.numel(), float(scale), out.data_ptr(), _stream(x)))
     return out
 
@@ -166,7 +183,17 @@ def sum_f64(x, scale=1.0):
 FUSED_MODE = "auto"          # "auto" | "resident" | "stream"
 
 
+_PLAN_CACHE = {}
+
+
 def fused_plan(logits, n_vol, D, H, W):
+    key = (logits.dtype, n_vol, D, H, W)
+    if key not in _PLAN_CACHE:
+        _PLAN_CACHE[key] = _fused_plan(logits, n_vol, D, H, W)
+    return _PLAN_CACHE[key]
+
+
+def _fused_plan(logits, n_vol, D, H, W):
     """Which launch computes loss + gradient fastest for this geometry, from B200 measurements
     (profiles/r1_configs.md): "resident" (persistent on-chip launch, one HBM read + one write)
     for the fp32 geometry it is tuned for -- 256-byte rows, volumes <= 1 MiB, i.e. 21x64^3;
@@ -226,7 +253,7 @@ def joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm):
     stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
     terms = torch.empty((n_vol * 3,), dtype=torch.float64, device=dev)
     dlogits = torch.empty_like(logits)
-    with torch.cuda.device(dev):
+    with _on(dev):
         ws = _workspace(dev, need)
         with _launch("joint_loss_resident", logits):
             check(lib.hipe_joint_loss_resident(
@@ -259,7 +286,7 @@ def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, varian
     stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
     terms = torch.empty((n_vol * 3,), dtype=torch.float64, device=dev)
     dlogits = torch.empty_like(logits)
-    with torch.cuda.device(dev), _launch("joint_loss_fused", logits):
+    with _on(dev), _launch("joint_loss_fused", logits):
         check(_lib.load().hipe_joint_loss_fused(
             logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
             coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), dlogits.data_ptr(),
@@ -282,7 +309,7 @@ def procrustes(X, Y, mode=0, optimal_scale=True, want=("Z", "pa_dist", "raw_dist
     shapes = {"d": (N,), "Z": (N, J, 3), "T": (N, 3, 3), "b": (N,), "c": (N, 3), "pa_dist": (N, J),
               "raw_dist": (N, J)}
     out = {k: torch.empty(shapes[k], dtype=torch.float64, device=X.device) for k in want}
-    with torch.cuda.device(X.device), _launch("procrustes", X):
+    with _on(X.device), _launch("procrustes", X):
         check(_lib.load().hipe_procrustes_batched(
             X.data_ptr(), Y.data_ptr(), N, J, int(mode), 1 if optimal_scale else 0,
             _ptr(out.get("d")), _ptr(out.get("Z")), _ptr(out.get("T")), _ptr(out.get("b")),
@@ -311,7 +338,7 @@ def keypoint_measures(dist, val_min, val_max, steps, vis=None):
     ws = torch.empty((max(need, 8) // 8,), dtype=torch.float64, device=d.device)
     summary = torch.empty((3,), dtype=torch.float64, device=d.device)
     curve = torch.empty((max(steps, 0),), dtype=torch.float64, device=d.device)
-    with torch.cuda.device(d.device), _launch("keypoint_measures", d):
+    with _on(d.device), _launch("keypoint_measures", d):
         check(lib.hipe_keypoint_measures(d.data_ptr(), _ptr(v), N, K, float(val_min), float(val_max), steps,
                                          summary.data_ptr(), curve.data_ptr(), ws.data_ptr(), ws.numel() * 8,
                                          _stream(d)))
@@ -363,7 +390,7 @@ def patch_to_camera(coords, N, J, tprime, K, trans=None, bbox=None, R=None, bone
     common = (coords.data_ptr(), kind, stride, N, J, float(patch[0]), float(patch[1]), _ptr(trans), _ptr(bbox),
               float(box_scale), float(dst[0]), float(dst[1]), tprime.data_ptr(), K.data_ptr(), _ptr(R),
               _ptr(bone_len), int(bone[0]), int(bone[1]))
-    with torch.cuda.device(dev):
+    with _on(dev):
         if gt is None:
             if set(want) - {"img", "cam"}:
                 raise ValueError("Z / pa_dist / raw_dist need gt")
@@ -446,10 +473,13 @@ class FusedJointLossFunction(torch.autograd.Function):
     def backward(ctx, grad_loss, _grad_coords):
         (dlogits,) = ctx.saved_tensors
         # in place, on device, no host sync; the kernel returns at once when the scalar is 1
-        gs = grad_loss.to(device=dlogits.device, dtype=torch.float32).reshape(1).contiguous()
-        with torch.cuda.device(dlogits.device), _launch("scale_inplace", dlogits):
-            check(_lib.load().hipe_scale_inplace(dlogits.data_ptr(), _logits_code(dlogits), dlogits.numel(),
-                                                 gs.data_ptr(), _stream(dlogits)))
+        gs = grad_loss
+        if gs.device != dlogits.device or gs.dtype not in (torch.float32, torch.float64) or not gs.is_contiguous():
+            gs = gs.to(device=dlogits.device, dtype=torch.float32).reshape(1).contiguous()
+        with _on(dlogits.device), _launch("scale_inplace", dlogits):
+            check(_lib.load().hipe_scale_inplace_s(dlogits.data_ptr(), _logits_code(dlogits), dlogits.numel(),
+                                                   gs.data_ptr(), _lib.F32 if gs.dtype == torch.float32 else _lib.F64,
+                                                   _stream(dlogits)))
         return dlogits.view(ctx.in_shape), None, None, None, None, None, None, None
 
 
@@ -470,7 +500,7 @@ class Orthonormalize3Function(torch.autograd.Function):
         code = _lib.F32 if a.dtype == torch.float32 else _lib.F64
         out = torch.empty_like(a)
         aux = torch.empty((n, 21), dtype=torch.float64, device=a.device)
-        with torch.cuda.device(a.device), _launch("orthonormalize3_fwd", a):
+        with _on(a.device), _launch("orthonormalize3_fwd", a):
             check(_lib.load().hipe_orthonormalize3_fwd(a.data_ptr(), code, n, out.data_ptr(), aux.data_ptr(), _stream(a)))
         ctx.save_for_backward(aux)
         ctx.code = code
@@ -482,6 +512,6 @@ class Orthonormalize3Function(torch.autograd.Function):
         g = grad.contiguous()
         n = g.numel() // 9
         d = torch.empty_like(g)
-        with torch.cuda.device(g.device), _launch("orthonormalize3_bwd", g):
+        with _on(g.device), _launch("orthonormalize3_bwd", g):
             check(_lib.load().hipe_orthonormalize3_bwd(g.data_ptr(), ctx.code, n, aux.data_ptr(), d.data_ptr(), _stream(g)))
         return d

@@ -146,6 +146,10 @@ HIPE_API int hipe_joint_loss_resident(const void* logits_dev, int dtype, long lo
  * launch already produced, without a host synchronisation.
  */
 HIPE_API int hipe_scale_inplace(void* x_dev, int dtype, long long n, const float* gscale_dev, void* stream);
+/* the same with the scalar read as HIPE_F32 or HIPE_F64 (the loss, hence its gradient, is fp64 in the
+ * reference: no conversion launch in front) */
+HIPE_API int hipe_scale_inplace_s(void* x_dev, int dtype, long long n, const void* gscale_dev, int gscale_dtype,
+                         void* stream);
 
 /* Deterministic fp64 sum of n doubles into out_dev[0] (times `scale`). */
 HIPE_API int hipe_sum_f64(const double* in_dev, long long n, double scale, double* out_dev, void* stream);

@@ -193,6 +193,6 @@ def test_default_module_picks_the_measured_fastest_launch():
     y = _cuda(hm).requires_grad_(True)
     l2 = L.JointLocationLoss(fused=False)(y, _cuda(gt), _cuda(vis))
     l2.backward()
-    assert abs(loss.item() - l2.item()) <= 1e-9 * abs(l2.item())
+    assert abs(loss.item() - l2.item()) <= 1e-6 * abs(l2.item())   # two kernels, fp32 coordinates
     scale = y.grad.view(16 * 21, -1).abs().amax(dim=1, keepdim=True)
     assert ((x.grad - y.grad).view(16 * 21, -1).abs() <= 2e-5 * scale + 1e-12).all()
