@@ -370,8 +370,9 @@ def run_ours(a):
             "warmup": max(a.warmup, 3), "ms_per_step": ms / a.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
             "config": {"workload": workload_name(a), "global_batch": B * world, "volumes_per_step": n_vol * world,
-                       "volume": [D, D, D], "parallelism": "batch-sharded x%d, one packed all-gather per step" % world
-                       if world > 1 else "single GPU",
+                       "volume": [D, D, D], "parallelism": ("batch-sharded x%d, one exchange per step (%s)" % (
+                           world, "hipe_peer_exchange: one kernel over NVLink peer memory" if getattr(crit, "exchange", None) == "peer"
+                           else "NCCL all-gather of the packed records")) if world > 1 else "single GPU",
                        "l2": "inputs larger than L2: %d rotating %.2f GB logit buffers per GPU" % (NBUF, n_vol * V * esz / 1e9),
                        "regime": "peaked (A=12, sigma=2) + N(0,1)", "launch_plan": ("single launch: loss + gradient, one HBM read + one write per volume (%s)" % dom)
                        if single_launch else "two launches: forward (read V) + recompute backward (read V, write V)",

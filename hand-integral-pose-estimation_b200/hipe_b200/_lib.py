@@ -40,6 +40,9 @@ SIGNATURES = {
     "hipe_keypoint_measures": (_i, [_vp, _vp, _ll, _i, _d, _d, _i, _vp, _vp, _vp, _ll, _vp]),
     "hipe_orthonormalize3_fwd": (_i, [_vp, _i, _ll, _vp, _vp, _vp]),
     "hipe_orthonormalize3_bwd": (_i, [_vp, _i, _ll, _vp, _vp, _vp]),
+    "hipe_peer_exchange_reclen": (_ll, [_ll, _i]),
+    "hipe_peer_exchange_bytes": (_ll, [_i, _ll, _i]),
+    "hipe_peer_exchange": (_i, [_vp, _d, _vp, _ll, _i, _vp, _i, _i, _c.c_ulonglong, _d, _vp, _vp, _vp, _vp, _d, _vp]),
     "hipe_joint_location_loss_host": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp,
                                            _vp, _ll]),
     "hipe_procrustes_host": (_i, [_vp, _vp, _ll, _i, _i, _i, _vp, _vp, _vp]),

@@ -119,6 +119,61 @@ def _local_cuda_loss(heatmap_out, gt_coord, gt_vis):
     return loss_sum, coords
 
 
+class _PeerExchange:
+    """The step's exchange as ONE kernel over NVLink peer memory (hipe_peer_exchange): every rank
+    stores its record into all peers' symmetric buffers, publishes a sequence number, waits for
+    the peers' and combines -- no NCCL launch, no stream hand-off, no pack / unpack launches.
+    The buffers come from torch.distributed._symmetric_memory (plumbing: allocation + rendezvous)."""
+
+    def __init__(self, world, rank, b, k, device, group):
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        lib = _lib.load()
+        self.world, self.rank, self.b, self.k, self.group = world, rank, b, k, group
+        nbytes = lib.hipe_peer_exchange_bytes(world, b, k)
+        if nbytes <= 0:
+            raise RuntimeError("peer exchange: unsupported world / shard size")
+        self.buf = symm.empty(nbytes // 8, dtype=torch.float64, device=device)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, dist.group.WORLD if group is None else group)
+        self.peers_dev = int(self.hdl.buffer_ptrs_dev)
+        self.err = torch.zeros(1, dtype=torch.int32, device=device)
+        self.value = torch.empty(2, dtype=torch.float64, device=device)      # alternating outputs
+        self.coords_all = [torch.empty((world * b, k), dtype=torch.float64, device=device) for _ in range(2)]
+        self.seq = 0
+        torch.cuda.synchronize(device)
+        dist.barrier(group)                    # every buffer is zeroed before anyone's first store
+
+    def run(self, loss_scalar, in_scale, coords, value_scale):
+        from . import _lib, ops
+        self.seq += 1
+        slot = self.seq & 1
+        out = self.value[slot:slot + 1]
+        call = self.coords_all[slot]
+        with ops._launch("peer_exchange", coords):
+            _lib.check(_lib.load().hipe_peer_exchange(
+                loss_scalar.data_ptr(), float(in_scale), coords.data_ptr(), self.b, self.k, self.peers_dev,
+                self.world, self.rank, self.seq, float(value_scale), out.data_ptr(), None, call.data_ptr(),
+                self.err.data_ptr(), 20.0, torch.cuda.current_stream(coords.device).cuda_stream))
+        return out.view(()), call
+
+    def timed_out(self):
+        return bool(self.err.item() != 0)
+
+
+def _peer_exchange_wanted(group, device):
+    """HIPE_EXCHANGE = peer | nccl | auto (default: peer memory on CUDA with the NCCL backend)."""
+    import os
+    mode = os.environ.get("HIPE_EXCHANGE", "auto")
+    if mode == "nccl" or device.type != "cuda":
+        return False
+    try:
+        backend = dist.get_backend(group)
+    except Exception:
+        return False
+    return mode == "peer" or "nccl" in str(backend)
+
+
 def _local_cuda_loss_fused(heatmap_out, gt_coord, gt_vis, norm):
     """(norm * loss_sum_local [differentiable], coords) from ONE launch that also stores the heatmap
     gradient already scaled by `norm` (ops.FusedJointLossFunction), so backward is a hand-over."""
@@ -165,6 +220,32 @@ class ShardedJointLocationLoss(nn.Module):
         self._coords = None
         self._coords64 = None
         self._xch = None
+        self._peer = None            # None = not tried yet, False = unavailable (NCCL is used)
+        self.exchange = None         # "peer" | "nccl": what the last step used
+
+    def _peer_exchange(self, world, b, k, device):
+        """The peer-memory exchange object for this geometry, or None.  Every rank must reach the same
+        decision: success is agreed on with one MIN all-reduce at set-up time."""
+        if self._peer is False:
+            return None
+        p = self._peer
+        if p is not None and (p.world, p.b, p.k) == (world, b, k):
+            return p
+        if not _peer_exchange_wanted(self.group, device):
+            self._peer = False
+            return None
+        ok, obj = 1, None
+        try:
+            obj = _PeerExchange(world, dist.get_rank(self.group), b, k, device, self.group)
+        except Exception as e:                           # no symmetric memory / P2P on this box
+            ok, self._peer_error = 0, repr(e)
+        t = torch.tensor([ok], dtype=torch.int32, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
+        if int(t.item()) == 0:
+            self._peer = False
+            return None
+        self._peer = obj
+        return obj
 
     @property
     def coords(self):
@@ -209,14 +290,27 @@ class ShardedJointLocationLoss(nn.Module):
             b_max = int(t.item())
         if counts is not None and b_local > 0 and all(c == b_local for c in counts):
             # fast path: equal shards known a priori (the training loop's case)
+            denom = float(world * b_local if self.size_average else world)
+            px = self._peer_exchange(world, b_local, k, coords.device) if coords.is_cuda and \
+                coords.dtype == torch.float32 and self.local_fn is _local_cuda_loss else None
             with torch.no_grad():
-                x = self._xch
-                if x is None or (x.world, x.b, x.k) != (world, b_local, k) or x.send.device != coords.device:
-                    x = self._xch = _Exchange(world, b_local, k, coords.device)
-                sums, allc = x.run(loss_sum.detach(), coords.detach(), self.group)
-                # mean over replicas of sum / len (balanced_parallel.py:127, loss.py:88-89), summed in
-                # rank order by one deterministic reduction of `world` values
-                value = sums.sum() / float(world * b_local if self.size_average else world)
+                if px is not None:
+                    # one kernel over NVLink peer memory: store to all peers, flag, wait, combine
+                    src = (scaled if scaled is not None else loss_sum).detach()
+                    if src.dtype != torch.float64:
+                        src = src.to(torch.float64)
+                    value, allc = px.run(src, (1.0 / norm) if scaled is not None else 1.0,
+                                         coords.detach().contiguous(), 1.0 / denom)
+                    self.exchange = "peer"
+                else:
+                    x = self._xch
+                    if x is None or (x.world, x.b, x.k) != (world, b_local, k) or x.send.device != coords.device:
+                        x = self._xch = _Exchange(world, b_local, k, coords.device)
+                    sums, allc = x.run(loss_sum.detach(), coords.detach(), self.group)
+                    # mean over replicas of sum / len (balanced_parallel.py:127, loss.py:88-89), summed in
+                    # rank order by one deterministic reduction of `world` values
+                    value = sums.sum() / denom
+                    self.exchange = "nccl"
             self._coords, self._coords64 = None, (allc.reshape(world, b_local, k), coords.dtype)
             if scaled is not None:
                 return _ValueWithGradOf.apply(scaled, value)

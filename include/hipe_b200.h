@@ -238,6 +238,27 @@ HIPE_API int hipe_orthonormalize3_bwd(const void* G_dev, int dtype, long long N,
                              void* dA_dev, void* stream);
 
 /*
+ * The exchange step of the batch-sharded path as ONE kernel over NVLink peer memory: replaces
+ * Reduce.apply(*outputs) / len(outputs) (common/nets/balanced_parallel.py:46-55,127) and the
+ * gather of the predicted joints.  Every rank calls it once per step with the same `seq`
+ * (1, 2, 3, ...); rank r stores [loss_in[0]*in_scale, B, coords (B x K)] into slot r of every
+ * peer's buffer, publishes `seq`, waits (at most timeout_s, default 20 s) for all peers, and writes
+ *   value_out[0] = value_scale * sum_r loss_sum_r   (fixed rank order, identical on every rank)
+ *   sums_out[world] (nullable), coords_all_dev[world * B * K] doubles (nullable)
+ *   peers_dev : DEVICE array of `world` pointers, entry p = rank p's symmetric buffer of
+ *               hipe_peer_exchange_bytes(world, B, K) bytes (zeroed once before the first step),
+ *               mapped into this process (torch.distributed._symmetric_memory / cudaIpc)
+ *   err_dev   : set to 1 if a peer did not arrive in time (value_out is then NaN)   (nullable)
+ * Equal B on every rank (the training loop's equal shards); other cases use NCCL.
+ */
+HIPE_API long long hipe_peer_exchange_reclen(long long B, int K);
+HIPE_API long long hipe_peer_exchange_bytes(int world, long long B, int K);
+HIPE_API int hipe_peer_exchange(const double* loss_in_dev, double in_scale, const float* coords_dev, long long B,
+                       int K, void* const* peers_dev, int world, int rank, unsigned long long seq,
+                       double value_scale, double* value_out_dev, double* sums_out_dev,
+                       double* coords_all_dev, unsigned* err_dev, double timeout_s, void* stream);
+
+/*
  * Host-buffer convenience entry points (synchronous).
  * hipe_joint_location_loss_host: JointLocationLoss forward (+ backward when dlogits_host or
  * dlogits_dev is non-NULL) on host logits, streamed to the current device in chunks of

@@ -21,7 +21,7 @@ if os.path.exists(lp):
             pass
     tot = sum(sum(v) for v in agg.values())
     with open(os.path.join(out, "%s_launches.md" % tag), "w") as f:
-        f.write("# ncu launch list of `python bench.py --steps 20 --warmup 3 --no-e2e --no-cpu-baseline`\n\n"
+        f.write("# ncu launch list of `python bench.py --steps 20 --warmup 3 --no-e2e --no-cpu-baseline` (%s)\n\n" % tag +
                 "`ncu --metrics gpu__time_duration.sum --clock-control none -k regex:k_stream|k_l1|...` on one B200; "
                 "per-launch times are cold-cache and serialised, so only the SHARES are comparable with the "
                 "CUDA-event numbers in the bench line.\n\n| kernel | grid | block | launches | mean us | share |\n|---|---|---|---|---|---|\n")
@@ -42,7 +42,10 @@ WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
 traffic_path = os.path.join(out, "traffic.json")
 traffic = json.load(open(traffic_path)) if os.path.exists(traffic_path) else {}
 md = ["# ncu --set full captures (%s), one launch each, B200, `--clock-control none`\n" % tag]
-for name, key, cfgkey in [("%s_fwd_f32" % tag, "softargmax_fwd", "f32_64_B64"), ("%s_fwd_bf16" % tag, "softargmax_fwd", "bf16_64_B64"),
+BF16_B = os.environ.get("HIPE_NCU_BF16_B", "64")     # batch the bf16 forward capture was taken at
+for name, key, cfgkey in [("%s_resident_f32" % tag, "resident", "f32_64_B64"),
+                          ("%s_fwd_f32" % tag, "softargmax_fwd", "f32_64_B64"),
+                          ("%s_fwd_bf16" % tag, "softargmax_fwd", "bf16_64_B%s" % BF16_B),
                           ("%s_bwd_f32" % tag, "softargmax_bwd", "f32_64_B64"), ("%s_fused_f32" % tag, "fused", "f32_64_B64")]:
     rep = os.path.join(ROOT, "gpurun_out", name + ".ncu-rep")
     if not os.path.exists(rep):

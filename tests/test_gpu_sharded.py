@@ -26,11 +26,30 @@ def _worker(rank, world, port, B, out_dir):
         crit = PL.ShardedJointLocationLoss(global_batch=B)
         loss = crit(x, torch.as_tensor(gt[lo:hi]).cuda(), torch.as_tensor(vis[lo:hi]).cuda())
         loss.backward()
+        # several more steps through the same exchange object (sequence numbers, both parities), then
+        # the NCCL form of the same step for comparison
+        vals = []
+        for _ in range(5):
+            x2 = torch.as_tensor(hm[lo:hi]).cuda().requires_grad_(True)
+            l2 = crit(x2, torch.as_tensor(gt[lo:hi]).cuda(), torch.as_tensor(vis[lo:hi]).cuda())
+            l2.backward()
+            vals.append(l2.item())
+        peer_used = crit.exchange
+        peer_err = bool(crit._peer.timed_out()) if crit._peer else False
+        os.environ["HIPE_EXCHANGE"] = "nccl"
+        crit_n = PL.ShardedJointLocationLoss(global_batch=B)
+        x3 = torch.as_tensor(hm[lo:hi]).cuda().requires_grad_(True)
+        l3 = crit_n(x3, torch.as_tensor(gt[lo:hi]).cuda(), torch.as_tensor(vis[lo:hi]).cuda())
+        l3.backward()
+        os.environ.pop("HIPE_EXCHANGE")
         X, Y = synth.procrustes_pairs(101, seed=4)
         l2, h2 = PL.shard_bounds(101, world, rank)
         pa, raw = PL.sharded_pa_mpjpe(X[l2:h2], Y[l2:h2])
         np.savez(os.path.join(out_dir, "r%d.npz" % rank), loss=loss.item(), coords=crit.coords.cpu().numpy(),
-                 grad=x.grad.cpu().numpy(), pa=pa.item(), raw=raw.item())
+                 grad=x.grad.cpu().numpy(), pa=pa.item(), raw=raw.item(), repeats=np.array(vals),
+                 exchange=np.array(peer_used), exchange_n=np.array(crit_n.exchange), peer_err=np.array(peer_err),
+                 loss_n=l3.item(), coords_n=crit_n.coords.cpu().numpy(), grad_n=x3.grad.cpu().numpy(),
+                 peer_error=np.array(getattr(crit, "_peer_error", "")))
     finally:
         dist.destroy_process_group()
 
@@ -50,6 +69,15 @@ def test_sharded_criterion_nccl_world2(tmp_path):
     ref_g = O.joint_location_loss_grad(hm, gt, vis)
     outs = [np.load(os.path.join(str(tmp_path), "r%d.npz" % r)) for r in range(world)]
     assert outs[0]["loss"] == outs[1]["loss"]
+    for o in outs:
+        # the NVLink peer-memory exchange is the one that ran, it never timed out, repeated steps give
+        # the same bits, and the NCCL form of the step agrees
+        assert str(o["exchange"]) == "peer", "peer exchange unavailable: %s" % o["peer_error"]
+        assert str(o["exchange_n"]) == "nccl" and not bool(o["peer_err"])
+        assert (o["repeats"] == o["loss"]).all()
+        assert abs(o["loss_n"] - o["loss"]) <= 1e-14 * abs(o["loss"])
+        np.testing.assert_array_equal(o["coords_n"], o["coords"])
+        np.testing.assert_array_equal(o["grad_n"], o["grad"])
     assert abs(outs[0]["loss"] - ref_loss) <= 1e-5 * ref_loss
     for r in range(world):
         np.testing.assert_array_equal(outs[r]["coords"], outs[0]["coords"])
