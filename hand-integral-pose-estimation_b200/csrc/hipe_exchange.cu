@@ -44,16 +44,32 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 
 __global__ void __launch_bounds__(kXT)
-    k_peer_exchange(const double* __restrict__ loss_in, double in_scale, const float* __restrict__ coords, long long B,
+    k_peer_exchange(const double* __restrict__ loss_in, long long n_in, double in_scale, const float* __restrict__ coords, long long B,
                     int K, double* const* __restrict__ peers, int world, int rank, unsigned long long seq,
                     long long reclen, double value_scale, double* __restrict__ value_out,
                     double* __restrict__ sums_out, double* __restrict__ coords_all, unsigned* __restrict__ err,
                     unsigned long long timeout_ns) {
     __shared__ int timed_out;
+    __shared__ double red[32];
+    __shared__ double my_sum_sh;
     const int par = (int)(seq & 1ull);
     const long long n = B * K;
-    const double my_sum = loss_in[0] * in_scale;
-    if (threadIdx.x == 0) timed_out = 0;
+    // 0. this rank's loss sum, in the fixed order of k_sum_f64 (thread-strided partials -> warp
+    //    shuffles -> 32 warp partials)
+    {
+        double acc = 0.0;
+        for (long long i = threadIdx.x; i < n_in; i += kXT) acc += loss_in[i];
+        acc = warp_sum(acc);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+        if (threadIdx.x == 0) timed_out = 0;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            double r = warp_sum(red[threadIdx.x]);
+            if (threadIdx.x == 0) my_sum_sh = r * in_scale;
+        }
+        __syncthreads();
+    }
+    const double my_sum = my_sum_sh;
     // 1. my record into slot [par][rank] of every peer (own buffer included)
     for (int p = 0; p < world; ++p) {
         double* dst = peers[p] + ((long long)par * world + rank) * reclen;
@@ -127,16 +143,18 @@ extern "C" long long hipe_peer_exchange_bytes(int world, long long B, int K) {
     return 8ll * (2ll * world * reclen + 2ll * world);
 }
 
-extern "C" int hipe_peer_exchange(const double* loss_in, double in_scale, const float* coords, long long B, int K,
+extern "C" int hipe_peer_exchange(const double* loss_in, long long n_in, double in_scale, const float* coords,
+                                  long long B, int K,
                                   void* const* peers_dev, int world, int rank, unsigned long long seq,
                                   double value_scale, double* value_out, double* sums_out, double* coords_all,
                                   unsigned* err, double timeout_s, void* stream) {
     if (!loss_in || !coords || !peers_dev || !value_out) return HIPE_E_NULL;
-    if (world <= 0 || world > kXMaxWorld || rank < 0 || rank >= world || B <= 0 || K <= 0 || seq == 0) return HIPE_E_SHAPE;
+    if (world <= 0 || world > kXMaxWorld || rank < 0 || rank >= world || B <= 0 || K <= 0 || seq == 0 || n_in <= 0)
+        return HIPE_E_SHAPE;
     const long long reclen = hipe_peer_exchange_reclen(B, K);
     const unsigned long long tns = (unsigned long long)((timeout_s > 0 ? timeout_s : 20.0) * 1e9);
     k_peer_exchange<<<1, kXT, 0, static_cast<cudaStream_t>(stream)>>>(
-        loss_in, in_scale, coords, B, K, reinterpret_cast<double* const*>(peers_dev), world, rank, seq, reclen,
+        loss_in, n_in, in_scale, coords, B, K, reinterpret_cast<double* const*>(peers_dev), world, rank, seq, reclen,
         value_scale, value_out, sums_out, coords_all, err, tns);
     return (int)cudaGetLastError();
 }

@@ -458,19 +458,25 @@ class FusedJointLossFunction(torch.autograd.Function):
     gradient is not 1."""
 
     @staticmethod
-    def forward(ctx, heatmap_out, gt, vis, num_joints, D, H, W, norm):
+    def forward(ctx, heatmap_out, gt, vis, num_joints, D, H, W, norm, reduce_loss=True):
+        """-> (loss, coords (B, 3J), loss_terms (B*3J,) fp64).  reduce_loss=False leaves the scalar
+        unwritten (a carrier for the gradient only): the sharded path sums the terms inside its
+        exchange kernel instead of a separate launch."""
         B = heatmap_out.shape[0]
         n_vol = B * num_joints
         coords, _, _, terms, dlogits = joint_loss_fused(heatmap_out, n_vol, D, H, W, gt, vis, norm)
-        loss = sum_f64(terms, norm)
+        out_dtype = torch.promote_types(torch.float32, torch.promote_types(gt.dtype, vis.dtype))
+        if reduce_loss:
+            loss = sum_f64(terms, norm).to(out_dtype)
+        else:
+            loss = torch.empty((), dtype=out_dtype, device=terms.device)
         ctx.save_for_backward(dlogits)
         ctx.in_shape = heatmap_out.shape
-        out_dtype = torch.promote_types(torch.float32, torch.promote_types(gt.dtype, vis.dtype))
-        ctx.mark_non_differentiable(coords)
-        return loss.to(out_dtype), coords.view(B, num_joints * 3)
+        ctx.mark_non_differentiable(coords, terms)
+        return loss, coords.view(B, num_joints * 3), terms
 
     @staticmethod
-    def backward(ctx, grad_loss, _grad_coords):
+    def backward(ctx, grad_loss, _grad_coords, _grad_terms):
         (dlogits,) = ctx.saved_tensors
         # in place, on device, no host sync; the kernel returns at once when the scalar is 1
         gs = grad_loss
@@ -480,7 +486,7 @@ class FusedJointLossFunction(torch.autograd.Function):
             check(_lib.load().hipe_scale_inplace_s(dlogits.data_ptr(), _logits_code(dlogits), dlogits.numel(),
                                                    gs.data_ptr(), _lib.F32 if gs.dtype == torch.float32 else _lib.F64,
                                                    _stream(dlogits)))
-        return dlogits.view(ctx.in_shape), None, None, None, None, None, None, None
+        return dlogits.view(ctx.in_shape), None, None, None, None, None, None, None, None
 
 
 class Orthonormalize3Function(torch.autograd.Function):

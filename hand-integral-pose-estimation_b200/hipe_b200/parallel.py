@@ -152,7 +152,8 @@ class _PeerExchange:
         call = self.coords_all[slot]
         with ops._launch("peer_exchange", coords):
             _lib.check(_lib.load().hipe_peer_exchange(
-                loss_scalar.data_ptr(), float(in_scale), coords.data_ptr(), self.b, self.k, self.peers_dev,
+                loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
+                self.peers_dev,
                 self.world, self.rank, self.seq, float(value_scale), out.data_ptr(), None, call.data_ptr(),
                 self.err.data_ptr(), 20.0, torch.cuda.current_stream(coords.device).cuda_stream))
         return out.view(()), call
@@ -174,17 +175,19 @@ def _peer_exchange_wanted(group, device):
     return mode == "peer" or "nccl" in str(backend)
 
 
-def _local_cuda_loss_fused(heatmap_out, gt_coord, gt_vis, norm):
-    """(norm * loss_sum_local [differentiable], coords) from ONE launch that also stores the heatmap
-    gradient already scaled by `norm` (ops.FusedJointLossFunction), so backward is a hand-over."""
+def _local_cuda_loss_fused(heatmap_out, gt_coord, gt_vis, norm, reduce_loss=True):
+    """(norm * loss_sum_local [differentiable], coords, loss terms) from ONE launch that also stores
+    the heatmap gradient already scaled by `norm` (ops.FusedJointLossFunction), so backward is a
+    hand-over.  reduce_loss=False: the scalar is only a gradient carrier (its value is unset)."""
     from nets.loss import FreiHandConfig
     from . import ops
     joint_num = int(gt_coord.shape[1] / 3)
     w, h = heatmap_out.shape[-1], heatmap_out.shape[-2]
     d = heatmap_out.shape[-3] // FreiHandConfig.num_joints
-    scaled, coords = ops.FusedJointLossFunction.apply(heatmap_out, gt_coord.to(torch.float64),
-                                                      gt_vis.to(torch.float64), joint_num, d, h, w, norm)
-    return scaled, coords
+    scaled, coords, terms = ops.FusedJointLossFunction.apply(heatmap_out, gt_coord.to(torch.float64),
+                                                             gt_vis.to(torch.float64), joint_num, d, h, w, norm,
+                                                             reduce_loss)
+    return scaled, coords, terms
 
 
 def _fused_plan(heatmap_out, gt_coord):
@@ -263,7 +266,7 @@ class ShardedJointLocationLoss(nn.Module):
     def forward(self, heatmap_out, gt_coord, gt_vis):
         world = dist.get_world_size(self.group)
         counts = None
-        scaled = None
+        scaled = terms = None
         if self.global_batch is not None:
             counts = [hi - lo for lo, hi in (shard_bounds(self.global_batch, world, r) for r in range(world))]
             b_local = heatmap_out.shape[0]
@@ -276,8 +279,12 @@ class ShardedJointLocationLoss(nn.Module):
                 # single-launch kernel can store the finished gradient (no scaling pass in backward)
                 live = sum(1 for c in counts if c > 0)
                 norm = 1.0 / (b_local * live) if self.size_average else 1.0 / live
-                scaled, coords = _local_cuda_loss_fused(heatmap_out, gt_coord, gt_vis, norm)
-                loss_sum = scaled.detach() / norm
+                equal = all(c == b_local for c in counts)
+                px = self._peer_exchange(world, b_local, int(gt_coord.shape[1]), heatmap_out.device) if equal else None
+                # with the peer exchange the loss terms are summed inside the exchange kernel
+                scaled, coords, terms = _local_cuda_loss_fused(heatmap_out, gt_coord, gt_vis, norm,
+                                                               reduce_loss=px is None)
+                loss_sum = scaled.detach() / norm if px is None else None
         if scaled is None:
             loss_sum, coords = self.local_fn(heatmap_out, gt_coord, gt_vis)
         b_local, k = coords.shape
@@ -295,12 +302,12 @@ class ShardedJointLocationLoss(nn.Module):
                 coords.dtype == torch.float32 and self.local_fn is _local_cuda_loss else None
             with torch.no_grad():
                 if px is not None:
-                    # one kernel over NVLink peer memory: store to all peers, flag, wait, combine
-                    src = (scaled if scaled is not None else loss_sum).detach()
+                    # one kernel over NVLink peer memory: (sum the loss terms,) store to all peers,
+                    # flag, wait, combine
+                    src = terms if terms is not None else loss_sum.detach()
                     if src.dtype != torch.float64:
                         src = src.to(torch.float64)
-                    value, allc = px.run(src, (1.0 / norm) if scaled is not None else 1.0,
-                                         coords.detach().contiguous(), 1.0 / denom)
+                    value, allc = px.run(src.reshape(-1), 1.0, coords.detach().contiguous(), 1.0 / denom)
                     self.exchange = "peer"
                 else:
                     x = self._xch

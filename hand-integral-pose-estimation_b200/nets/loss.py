@@ -70,7 +70,7 @@ class JointLocationLoss(nn.Module):
         if fused is None and torch.is_grad_enabled() and heatmap_out.requires_grad and heatmap_out.is_cuda:
             fused = ops.fused_plan(heatmap_out, B * joint_num, hm_depth, hm_height, hm_width) is not None
         if fused and torch.is_grad_enabled() and heatmap_out.requires_grad:
-            loss, _ = ops.FusedJointLossFunction.apply(heatmap_out, gt_coord, gt_vis, joint_num, hm_depth,
+            loss, _, _ = ops.FusedJointLossFunction.apply(heatmap_out, gt_coord, gt_vis, joint_num, hm_depth,
                                                        hm_height, hm_width, norm)
             return loss
         coord_out = softmax_integral_tensor(heatmap_out, joint_num, hm_width, hm_height, hm_depth)

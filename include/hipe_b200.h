@@ -241,7 +241,9 @@ HIPE_API int hipe_orthonormalize3_bwd(const void* G_dev, int dtype, long long N,
  * The exchange step of the batch-sharded path as ONE kernel over NVLink peer memory: replaces
  * Reduce.apply(*outputs) / len(outputs) (common/nets/balanced_parallel.py:46-55,127) and the
  * gather of the predicted joints.  Every rank calls it once per step with the same `seq`
- * (1, 2, 3, ...); rank r stores [loss_in[0]*in_scale, B, coords (B x K)] into slot r of every
+ * (1, 2, 3, ...); rank r stores [in_scale * sum(loss_in[0..n_in)), B, coords (B x K)] (the sum in
+ * the fixed order of hipe_sum_f64: n_in = 1 for a finished scalar, or the loss terms of
+ * hipe_joint_loss_fused / _resident) into slot r of every
  * peer's buffer, publishes `seq`, waits (at most timeout_s, default 20 s) for all peers, and writes
  *   value_out[0] = value_scale * sum_r loss_sum_r   (fixed rank order, identical on every rank)
  *   sums_out[world] (nullable), coords_all_dev[world * B * K] doubles (nullable)
@@ -253,8 +255,8 @@ HIPE_API int hipe_orthonormalize3_bwd(const void* G_dev, int dtype, long long N,
  */
 HIPE_API long long hipe_peer_exchange_reclen(long long B, int K);
 HIPE_API long long hipe_peer_exchange_bytes(int world, long long B, int K);
-HIPE_API int hipe_peer_exchange(const double* loss_in_dev, double in_scale, const float* coords_dev, long long B,
-                       int K, void* const* peers_dev, int world, int rank, unsigned long long seq,
+HIPE_API int hipe_peer_exchange(const double* loss_in_dev, long long n_in, double in_scale,
+                       const float* coords_dev, long long B, int K, void* const* peers_dev, int world, int rank, unsigned long long seq,
                        double value_scale, double* value_out_dev, double* sums_out_dev,
                        double* coords_all_dev, unsigned* err_dev, double timeout_s, void* stream);
 

@@ -8,10 +8,10 @@ import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
-J, D = 21, 16
+J = 21
 
 
-def _worker(rank, world, port, B, out_dir):
+def _worker(rank, world, port, B, out_dir, geom):
     import torch.distributed as dist
     from hipe_b200 import parallel as PL
     from tests import synth
@@ -19,7 +19,8 @@ def _worker(rank, world, port, B, out_dir):
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        hm = synth.heatmaps(B, J, D, D, D, "peaked", seed=42)
+        D, H, W = geom
+        hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=42)
         gt, vis = synth.targets(B, J, seed=42, zero_vis_frac=0.1)
         lo, hi = PL.shard_bounds(B, world, rank)
         x = torch.as_tensor(hm[lo:hi]).cuda().requires_grad_(True)
@@ -55,15 +56,17 @@ def _worker(rank, world, port, B, out_dir):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_sharded_criterion_nccl_world2(tmp_path):
+@pytest.mark.parametrize("geom", [(16, 16, 16), (32, 64, 64)], ids=["two-launch", "single-launch"])
+def test_sharded_criterion_nccl_world2(tmp_path, geom):
     import torch.multiprocessing as mp
     from oracle import integral_np as O
     from oracle import procrustes_np as P
     from tests import synth
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     B, world = 6, 2
-    mp.spawn(_worker, args=(world, port, B, str(tmp_path)), nprocs=world, join=True)
-    hm = synth.heatmaps(B, J, D, D, D, "peaked", seed=42).astype(np.float64)
+    D, H, W = geom
+    mp.spawn(_worker, args=(world, port, B, str(tmp_path), geom), nprocs=world, join=True)
+    hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=42).astype(np.float64)
     gt, vis = synth.targets(B, J, seed=42, zero_vis_frac=0.1)
     ref_loss, ref_c = O.joint_location_loss(hm, gt, vis, return_coords=True)      # equal shards: global sum / B
     ref_g = O.joint_location_loss_grad(hm, gt, vis)
@@ -83,8 +86,8 @@ def test_sharded_criterion_nccl_world2(tmp_path):
         np.testing.assert_array_equal(outs[r]["coords"], outs[0]["coords"])
         err = np.abs(outs[r]["coords"] - ref_c)
         assert (err <= 1e-5 * np.maximum(np.abs(ref_c), 0.5)).all()
-        g = outs[r]["grad"].reshape(-1, D ** 3)
-        rg = ref_g[r * 3:(r + 1) * 3].reshape(-1, D ** 3)
+        g = outs[r]["grad"].reshape(-1, D * H * W)
+        rg = ref_g[r * 3:(r + 1) * 3].reshape(-1, D * H * W)
         assert (np.abs(g - rg) <= 1e-5 * np.abs(rg).max(axis=1, keepdims=True) + 1e-12).all()
     X, Y = synth.procrustes_pairs(101, seed=4)
     rpa, rraw = P.pa_mpjpe(X, Y)
