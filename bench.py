@@ -274,6 +274,8 @@ def run_ours(a):
     ms, kern, launches, loss_value, sampler = timed(crit, a.steps, max(a.warmup, 3), True)
     value = world * n_vol * a.steps / (ms / 1e3)
     host_enqueue_ms = host_ms[0]
+    if loss_value != loss_value or abs(loss_value) == float("inf"):
+        raise RuntimeError("bench: the timed steps produced a non-finite loss (%r)" % loss_value)
     single_launch = ("joint_loss_resident" in kern) or ("joint_loss_fused" in kern)
     # the other launch plan, same buffers, same K: reported beside the primary, never as `value`
     alt = None

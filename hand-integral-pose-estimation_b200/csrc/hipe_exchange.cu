@@ -4,11 +4,12 @@
 // Replaces, per training step, what the reference does with Reduce.apply(*outputs) / len(outputs)
 // (common/nets/balanced_parallel.py:46-55,127) plus the gather of predicted joints: every rank
 // holds a record [ loss_sum_r , B_r , coords_r (B x 3J) ] and needs all of them.  Each rank's
-// kernel (1 CTA) stores its record straight into slot [parity][rank] of EVERY peer's symmetric
-// buffer (P2P stores through NVSwitch), publishes a monotonically increasing sequence number
-// into the peer's flag word with a system-scope release, then acquires the flags of all peers in
-// its own buffer and combines the world loss sums in fixed rank order -- bit-identical on every
-// rank.  ~32 KB per rank per step: latency-sized, so the point is launch count and the absence
+// kernel (one CTA per peer) stores its record straight into slot [parity][rank] of EVERY peer's
+// symmetric buffer (16-byte P2P stores through NVSwitch), publishes a monotonically increasing
+// sequence number into the peer's flag word with a system-scope release, acquires that peer's flag
+// in its own buffer, copies the record out, and the last CTA combines the world loss sums in fixed
+// rank order -- bit-identical on every rank.  (A first version did all peers from one CTA: 29 us
+// at 2 GPUs but 108 / 167 us at 4 / 8, i.e. serial in the world size.)  ~32 KB per rank per step: latency-sized, so the point is launch count and the absence
 // of stream hand-offs, not bandwidth.
 //
 // Buffer layout per rank (doubles unless noted), both parities:
@@ -21,7 +22,7 @@
 
 namespace hipe {
 
-constexpr int kXT = 1024;
+constexpr int kXT = 512;
 constexpr int kXMaxWorld = 64;
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
@@ -43,19 +44,25 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
     return t;
 }
 
+// grid = world CTAs: CTA p serves peer p (store + publish), waits for rank p's record, copies it out;
+// the last CTA to finish (atomic ticket) combines the `world` loss sums in rank order.  No CTA
+// waits on another CTA of this grid, so co-residency is not required for progress.
 __global__ void __launch_bounds__(kXT)
-    k_peer_exchange(const double* __restrict__ loss_in, long long n_in, double in_scale, const float* __restrict__ coords, long long B,
-                    int K, double* const* __restrict__ peers, int world, int rank, unsigned long long seq,
-                    long long reclen, double value_scale, double* __restrict__ value_out,
+    k_peer_exchange(const double* __restrict__ loss_in, long long n_in, double in_scale, const float* __restrict__ coords,
+                    long long B, int K, double* const* __restrict__ peers, int world, int rank,
+                    unsigned long long seq, long long reclen, double value_scale, double* __restrict__ value_out,
                     double* __restrict__ sums_out, double* __restrict__ coords_all, unsigned* __restrict__ err,
+                    double* __restrict__ scratch /* world sums */, unsigned* __restrict__ ticket,
                     unsigned long long timeout_ns) {
     __shared__ int timed_out;
     __shared__ double red[32];
     __shared__ double my_sum_sh;
+    __shared__ unsigned my_ticket;
+    const int p = blockIdx.x;                 // the peer this CTA serves / the rank it listens to
     const int par = (int)(seq & 1ull);
     const long long n = B * K;
-    // 0. this rank's loss sum, in the fixed order of k_sum_f64 (thread-strided partials -> warp
-    //    shuffles -> 32 warp partials)
+    // 0. this rank's loss sum, in a fixed order (thread-strided partials -> warp shuffles ->
+    //    kXT/32 warp partials); every CTA forms the same bits
     {
         double acc = 0.0;
         for (long long i = threadIdx.x; i < n_in; i += kXT) acc += loss_in[i];
@@ -64,66 +71,67 @@ __global__ void __launch_bounds__(kXT)
         if (threadIdx.x == 0) timed_out = 0;
         __syncthreads();
         if (threadIdx.x < 32) {
-            double r = warp_sum(red[threadIdx.x]);
+            double r = warp_sum((threadIdx.x < kXT / 32) ? red[threadIdx.x] : 0.0);
             if (threadIdx.x == 0) my_sum_sh = r * in_scale;
         }
         __syncthreads();
     }
-    const double my_sum = my_sum_sh;
-    // 1. my record into slot [par][rank] of every peer (own buffer included)
-    for (int p = 0; p < world; ++p) {
+    // 1. my record into slot [par][rank] of peer p (16-byte stores over NVLink; own buffer when p == rank)
+    {
         double* dst = peers[p] + ((long long)par * world + rank) * reclen;
-        if (threadIdx.x == 0) {
-            dst[0] = my_sum;
-            dst[1] = (double)B;
-        }
-        for (long long i = threadIdx.x; i < n; i += kXT) dst[2 + i] = (double)coords[i];
+        if (threadIdx.x == 0) *reinterpret_cast<double2*>(dst) = make_double2(my_sum_sh, (double)B);
+        const long long npair = n >> 1;
+        for (long long i = threadIdx.x; i < npair; i += kXT)
+            *reinterpret_cast<double2*>(dst + 2 + 2 * i) = make_double2((double)coords[2 * i], (double)coords[2 * i + 1]);
+        if ((n & 1) && threadIdx.x == 0) dst[2 + n - 1] = (double)coords[n - 1];
     }
     __threadfence_system();
     __syncthreads();
-    // 2. publish: flag[par][rank] of every peer <- seq
-    if (threadIdx.x < world) {
-        unsigned long long* f = reinterpret_cast<unsigned long long*>(peers[threadIdx.x] + 2ll * world * reclen) +
-                                (long long)par * world + rank;
-        st_release_sys_u64(f, seq);
-    }
-    // 3. wait for every peer's record in my own buffer (bounded by wall time, never hangs the GPU)
-    if (threadIdx.x < world) {
-        const unsigned long long* f = reinterpret_cast<const unsigned long long*>(peers[rank] + 2ll * world * reclen) +
-                                      (long long)par * world + threadIdx.x;
+    // 2. publish to peer p, 3. wait for rank p's record in my own buffer (bounded by wall time)
+    if (threadIdx.x == 0) {
+        unsigned long long* fp = reinterpret_cast<unsigned long long*>(peers[p] + 2ll * world * reclen) +
+                                 (long long)par * world + rank;
+        st_release_sys_u64(fp, seq);
+        const unsigned long long* fm = reinterpret_cast<const unsigned long long*>(peers[rank] + 2ll * world * reclen) +
+                                       (long long)par * world + p;
         const unsigned long long t0 = globaltimer_ns();
-        while (ld_acquire_sys_u64(f) < seq) {
+        while (ld_acquire_sys_u64(fm) < seq) {
             if (globaltimer_ns() - t0 > timeout_ns) {
                 timed_out = 1;
                 break;
             }
-            __nanosleep(64);
+            __nanosleep(32);
         }
     }
     __syncthreads();
-    if (timed_out) {
-        if (threadIdx.x == 0) {
-            if (err) atomicExch(err, 1u);
-            value_out[0] = __longlong_as_double(0x7ff8000000000000ll);
+    // 4. rank p's record -> ordinary tensors
+    const double* slot = peers[rank] + ((long long)par * world + p) * reclen;
+    if (!timed_out) {
+        if (coords_all) {
+            double* out = coords_all + (long long)p * n;
+            for (long long i = threadIdx.x; i < n; i += kXT) out[i] = ld_relaxed_sys_f64(slot + 2 + i);
         }
-        return;
+        if (threadIdx.x == 0) scratch[p] = ld_relaxed_sys_f64(slot);
+    } else if (threadIdx.x == 0) {
+        if (err) atomicExch(err, 1u);
+        scratch[p] = __longlong_as_double(0x7ff8000000000000ll);
     }
-    // 4. combine in fixed rank order; hand the gathered joints to an ordinary tensor
-    const double* mine = peers[rank] + (long long)par * world * reclen;
-    if (threadIdx.x == 0) {
+    // 5. last CTA out combines in fixed rank order
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) my_ticket = atomicAdd(ticket, 1u);
+    __syncthreads();
+    if (my_ticket == (unsigned)world - 1u && threadIdx.x == 0) {
+        __threadfence();
         double tot = 0.0;
         for (int r = 0; r < world; ++r) {
-            const double s = ld_relaxed_sys_f64(mine + r * reclen);
-            if (sums_out) sums_out[r] = s;
-            tot += s;
+            const double v = *reinterpret_cast<volatile double*>(scratch + r);
+            if (sums_out) sums_out[r] = v;
+            tot += v;
         }
         value_out[0] = tot * value_scale;
+        *ticket = 0u;                          // ready for the next launch (stream order)
     }
-    if (coords_all)
-        for (long long i = threadIdx.x; i < (long long)world * n; i += kXT) {
-            const long long r = i / n, j = i - r * n;
-            coords_all[i] = ld_relaxed_sys_f64(mine + r * reclen + 2 + j);
-        }
 }
 
 }  // namespace hipe
@@ -147,14 +155,15 @@ extern "C" int hipe_peer_exchange(const double* loss_in, long long n_in, double 
                                   long long B, int K,
                                   void* const* peers_dev, int world, int rank, unsigned long long seq,
                                   double value_scale, double* value_out, double* sums_out, double* coords_all,
-                                  unsigned* err, double timeout_s, void* stream) {
-    if (!loss_in || !coords || !peers_dev || !value_out) return HIPE_E_NULL;
+                                  unsigned* err, double* scratch, double timeout_s, void* stream) {
+    if (!loss_in || !coords || !peers_dev || !value_out || !scratch) return HIPE_E_NULL;
     if (world <= 0 || world > kXMaxWorld || rank < 0 || rank >= world || B <= 0 || K <= 0 || seq == 0 || n_in <= 0)
         return HIPE_E_SHAPE;
     const long long reclen = hipe_peer_exchange_reclen(B, K);
     const unsigned long long tns = (unsigned long long)((timeout_s > 0 ? timeout_s : 20.0) * 1e9);
-    k_peer_exchange<<<1, kXT, 0, static_cast<cudaStream_t>(stream)>>>(
+    // scratch: `world` doubles, then one 32-bit ticket (zero before the first launch)
+    k_peer_exchange<<<world, kXT, 0, static_cast<cudaStream_t>(stream)>>>(
         loss_in, n_in, in_scale, coords, B, K, reinterpret_cast<double* const*>(peers_dev), world, rank, seq, reclen,
-        value_scale, value_out, sums_out, coords_all, err, tns);
+        value_scale, value_out, sums_out, coords_all, err, scratch, reinterpret_cast<unsigned*>(scratch + world), tns);
     return (int)cudaGetLastError();
 }

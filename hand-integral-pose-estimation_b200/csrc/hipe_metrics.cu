@@ -158,6 +158,75 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+
+// ---------------------------------------------------------------------------------------
+// Per-volume softmax entropy: what main/generate_correlation_graph.py:116-141
+// gets from softmax_integral_tensor2 (common/nets/loss.py:61-67) -> .cpu() -> scipy.stats.entropy per
+// joint, without ever materialising the (B, J, V) probabilities or copying them to the host:
+//   H = -sum p ln p = ln L - ln2 * (sum e_i a_i) / L,   a_i = s_i log2e - fl(M log2e),  e_i = 2^a_i
+// with (M, L) the statistics the forward launch already produced.  One streaming read of the
+// volume (128-bit ld.global.nc, 4 loads in flight per thread), one CTA per volume, fp32 products
+// summed per thread in fp64, fixed-order block reduction.  HBM-bound: V*s bytes per volume.
+// ---------------------------------------------------------------------------------------
+constexpr int kET = 512;
+
+template <typename T>
+__global__ void __launch_bounds__(kET)
+    k_entropy(const unsigned char* __restrict__ in, long long n_vol, long long V, const float* __restrict__ stats,
+              double* __restrict__ entropy, int vec_ok) {
+    using V16 = Vec16<T>;
+    constexpr int VEC = V16::N;
+    __shared__ double red[kET / 32];
+    const long long vol = blockIdx.x;
+    const float M = stats[vol * 2 + 0];
+    const double Lsum = (double)stats[vol * 2 + 1];
+    const float ML = __fmul_rn(M, kLog2e);
+    const T* src = reinterpret_cast<const T*>(in) + vol * V;
+    double acc = 0.0;
+    long long done = 0;
+    if (vec_ok) {
+        const long long nvec = V / VEC;
+        const unsigned char* base = reinterpret_cast<const unsigned char*>(src);
+        for (long long i0 = 0; i0 < nvec; i0 += 4ll * kET) {
+            uint4 r[4];
+            bool ok[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long long i = i0 + (long long)u * kET + threadIdx.x;
+                ok[u] = i < nvec;
+                if (ok[u]) r[u] = ldg_stream(base + i * 16);
+            }
+            float part = 0.f;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (!ok[u]) continue;
+                float v[VEC];
+                V16::unpack(r[u], v);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    // clamp: a = -inf (a -inf logit) would give 0 * inf; 2^-200 flushes to 0 all the same
+                    const float a = fmaxf(fmaf(v[j], kLog2e, -ML), -200.f);
+                    part = fmaf(ex2(a), a, part);     // e * a in (-0.54, 0]
+                }
+            }
+            acc += (double)part;
+        }
+        done = nvec * VEC;
+    }
+    for (long long i = done + threadIdx.x; i < V; i += kET) {
+        const float a = fmaxf(fmaf(V16::to_f32(src[i]), kLog2e, -ML), -200.f);
+        acc += (double)(ex2(a) * a);
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double r = (threadIdx.x < kET / 32) ? red[threadIdx.x] : 0.0;
+        r = warp_sum(r);
+        if (threadIdx.x == 0) entropy[vol] = log(Lsum) - 0.6931471805599453 * r / Lsum;
+    }
+}
+
 }  // namespace hipe
 
 using namespace hipe;
@@ -182,5 +251,24 @@ extern "C" int hipe_keypoint_measures(const double* dist, const unsigned char* v
     double* pck = auc + K;
     k_keypoint_measures<<<K, kMT, 0, st>>>(dist, vis, N, K, val_min, val_max, steps, cnt, mean, med, auc, pck);
     k_measures_final<<<1, 256, 0, st>>>(cnt, mean, med, auc, pck, K, steps, summary, pck_curve);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int hipe_volume_entropy(const void* logits, int dtype, long long n_vol, int D, int H, int W,
+                                   const float* stats, double* entropy, void* stream) {
+    if (n_vol < 0 || D <= 0 || H <= 0 || W <= 0) return HIPE_E_SHAPE;
+    if (n_vol == 0) return 0;
+    if (!logits || !stats || !entropy) return HIPE_E_NULL;
+    if (dtype != HIPE_F32 && dtype != HIPE_BF16) return HIPE_E_DTYPE;
+    if (n_vol > 0x7fffffffll) return HIPE_E_SHAPE;
+    const long long V = (long long)D * H * W;
+    const int esz = dtype == HIPE_F32 ? 4 : 2;
+    if (reinterpret_cast<uintptr_t>(logits) % esz) return HIPE_E_ALIGN;
+    const int vec_ok = (reinterpret_cast<uintptr_t>(logits) % 16 == 0) && ((V * esz) % 16 == 0);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dtype == HIPE_F32)
+        k_entropy<float><<<(unsigned)n_vol, kET, 0, st>>>(static_cast<const unsigned char*>(logits), n_vol, V, stats, entropy, vec_ok);
+    else
+        k_entropy<__nv_bfloat16><<<(unsigned)n_vol, kET, 0, st>>>(static_cast<const unsigned char*>(logits), n_vol, V, stats, entropy, vec_ok);
     return (int)cudaGetLastError();
 }

@@ -22,6 +22,7 @@ SIGNATURES = {
     "hipe_softargmax_fwd": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp]),
     "hipe_softargmax_bwd": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "hipe_volume_softmax": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _i, _vp]),
+    "hipe_volume_entropy": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _vp]),
     "hipe_l1_loss_fwd": (_i, [_vp, _vp, _vp, _i, _ll, _i, _d, _vp, _vp, _vp]),
     "hipe_joint_loss_fused": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp,
                                    _i, _i, _vp]),
@@ -42,7 +43,7 @@ SIGNATURES = {
     "hipe_orthonormalize3_bwd": (_i, [_vp, _i, _ll, _vp, _vp, _vp]),
     "hipe_peer_exchange_reclen": (_ll, [_ll, _i]),
     "hipe_peer_exchange_bytes": (_ll, [_i, _ll, _i]),
-    "hipe_peer_exchange": (_i, [_vp, _ll, _d, _vp, _ll, _i, _vp, _i, _i, _c.c_ulonglong, _d, _vp, _vp, _vp, _vp, _d, _vp]),
+    "hipe_peer_exchange": (_i, [_vp, _ll, _d, _vp, _ll, _i, _vp, _i, _i, _c.c_ulonglong, _d, _vp, _vp, _vp, _vp, _vp, _d, _vp]),
     "hipe_joint_location_loss_host": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp,
                                            _vp, _ll]),
     "hipe_procrustes_host": (_i, [_vp, _vp, _ll, _i, _i, _i, _vp, _vp, _vp]),

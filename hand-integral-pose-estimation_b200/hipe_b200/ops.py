@@ -144,6 +144,22 @@ def volume_softmax(logits, n_vol, D, H, W, stats=None, cluster=None, variant=Non
     return out
 
 
+def volume_entropy(logits, n_vol, D, H, W, stats=None):
+    """-> (n_vol,) fp64 entropies (nats) of the per-volume softmax distributions, without the
+    probabilities ever existing (hipe_volume_entropy)."""
+    _need_cuda(logits, "heatmaps")
+    code = _logits_code(logits)
+    if not logits.is_contiguous():
+        logits = logits.contiguous()
+    if stats is None:
+        _, _, stats = softargmax_forward(logits, n_vol, D, H, W, True)
+    out = torch.empty((n_vol,), dtype=torch.float64, device=logits.device)
+    with _on(logits.device), _launch("volume_entropy", logits):
+        check(_lib.load().hipe_volume_entropy(logits.data_ptr(), code, n_vol, D, H, W, stats.data_ptr(),
+                                              out.data_ptr(), _stream(logits)))
+    return out
+
+
 def _targets(coords, gt, vis):
     tdt = torch.promote_types(gt.dtype, vis.dtype)
     if tdt not in _TGT:

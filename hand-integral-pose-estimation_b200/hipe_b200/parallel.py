@@ -138,6 +138,7 @@ class _PeerExchange:
         self.hdl = symm.rendezvous(self.buf, dist.group.WORLD if group is None else group)
         self.peers_dev = int(self.hdl.buffer_ptrs_dev)
         self.err = torch.zeros(1, dtype=torch.int32, device=device)
+        self.scratch = torch.zeros(world + 1, dtype=torch.float64, device=device)
         self.value = torch.empty(2, dtype=torch.float64, device=device)      # alternating outputs
         self.coords_all = [torch.empty((world * b, k), dtype=torch.float64, device=device) for _ in range(2)]
         self.seq = 0
@@ -155,7 +156,7 @@ class _PeerExchange:
                 loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
                 self.peers_dev,
                 self.world, self.rank, self.seq, float(value_scale), out.data_ptr(), None, call.data_ptr(),
-                self.err.data_ptr(), 20.0, torch.cuda.current_stream(coords.device).cuda_stream))
+                self.err.data_ptr(), self.scratch.data_ptr(), 20.0, torch.cuda.current_stream(coords.device).cuda_stream))
         return out.view(()), call
 
     def timed_out(self):

@@ -47,6 +47,16 @@ def softmax_integral_tensor2(preds, num_joints, hm_width, hm_height, hm_depth):
     return p.view(B, num_joints, -1)
 
 
+def softmax_entropy(preds, num_joints, hm_width, hm_height, hm_depth):
+    """Per-joint entropy (nats) of the volume softmax, shape (B, J) fp64: what
+    main/generate_correlation_graph.py:116-141 computes as scipy.stats.entropy over the rows of
+    softmax_integral_tensor2(...).cpu() -- here from the logits in one extra streaming read, no
+    probability tensor, no host copy.  (An addition next to the reference's names, not one of them.)"""
+    B = preds.shape[0]
+    h = ops.volume_entropy(preds.contiguous(), B * num_joints, hm_depth, hm_height, hm_width)
+    return h.view(B, num_joints)
+
+
 class JointLocationLoss(nn.Module):
     """loss.py:69-91.  When the heatmaps require a gradient the loss and `dlogits` can come out
     of ONE launch (one read + one write of each volume from HBM instead of two reads + one

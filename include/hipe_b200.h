@@ -95,6 +95,15 @@ HIPE_API int hipe_volume_softmax(const void* logits_dev, int dtype, long long n_
                         void* stream);
 
 /*
+ * Per-volume entropy of the softmax distribution, -sum p ln p: replaces the chain
+ * softmax_integral_tensor2 (common/nets/loss.py:61-67) -> .cpu().numpy() -> scipy.stats.entropy per
+ * joint of main/generate_correlation_graph.py:116-141.  One streaming read of the logits; needs the
+ * stats a forward call produced.  entropy_dev: n_vol doubles (nats).
+ */
+HIPE_API int hipe_volume_entropy(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
+                        const float* stats_dev, double* entropy_dev, void* stream);
+
+/*
  * L1 integral loss on coordinates: replaces common/nets/loss.py:86-89.
  *   coords_dev : B*K floats (K = 3*J);  gt_dev, vis_dev : B*K of tgt_dtype (HIPE_F32|HIPE_F64)
  *   norm       : the value the masked L1 sum is multiplied by (1/B for size_average)
@@ -251,6 +260,7 @@ HIPE_API int hipe_orthonormalize3_bwd(const void* G_dev, int dtype, long long N,
  *               hipe_peer_exchange_bytes(world, B, K) bytes (zeroed once before the first step),
  *               mapped into this process (torch.distributed._symmetric_memory / cudaIpc)
  *   err_dev   : set to 1 if a peer did not arrive in time (value_out is then NaN)   (nullable)
+ *   scratch_dev : world + 1 doubles of caller-owned device scratch, zeroed once before the first step
  * Equal B on every rank (the training loop's equal shards); other cases use NCCL.
  */
 HIPE_API long long hipe_peer_exchange_reclen(long long B, int K);
@@ -258,7 +268,8 @@ HIPE_API long long hipe_peer_exchange_bytes(int world, long long B, int K);
 HIPE_API int hipe_peer_exchange(const double* loss_in_dev, long long n_in, double in_scale,
                        const float* coords_dev, long long B, int K, void* const* peers_dev, int world, int rank, unsigned long long seq,
                        double value_scale, double* value_out_dev, double* sums_out_dev,
-                       double* coords_all_dev, unsigned* err_dev, double timeout_s, void* stream);
+                       double* coords_all_dev, unsigned* err_dev, double* scratch_dev, double timeout_s,
+                       void* stream);
 
 /*
  * Host-buffer convenience entry points (synchronous).

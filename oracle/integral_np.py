@@ -142,3 +142,16 @@ def combined_loss(heatmap_out, coord_teacher, gt_coord, gt_vis, labelled):
     sup = (np.abs(c[lab] - gt_coord[lab]) * gt_vis[lab]).sum() if lab.any() else 0.0
     uns = (np.abs(c[~lab] - teacher[~lab]) * gt_vis[~lab]).sum() if (~lab).any() else 0.0
     return (sup + uns) / len(c), compute_mpjpe(c, gt_coord), compute_mpjpe(teacher, gt_coord), sup, uns
+
+
+def softmax_entropy(logits, J, D, H, W):
+    """scipy.stats.entropy of each row of softmax_integral_tensor2's output
+    (main/generate_correlation_graph.py:116-141 on common/nets/loss.py:61-67): -sum p ln p per
+    (sample, joint) volume, float64.  (B, J)."""
+    x = np.asarray(logits, dtype=np.float64).reshape(logits.shape[0], J, D * H * W)
+    x = x - x.max(axis=2, keepdims=True)
+    e = np.exp(x)
+    p = e / e.sum(axis=2, keepdims=True)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t = np.where(p > 0, p * np.log(p), 0.0)
+    return -t.sum(axis=2)

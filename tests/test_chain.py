@@ -194,3 +194,43 @@ def test_masked_measures_kernel_vs_oracle(n):
     a = E.keypoint_measures(_cu(dist), 0.0, 0.05, 100)
     b = P.keypoint_measures_masked(dist, np.ones_like(vis), 0.0, 0.05, 100)
     np.testing.assert_allclose([a[0].item(), a[1].item(), a[2].item()], [b[0], b[1], b[2]], rtol=1e-12)
+
+
+# ------------------------------------------------------------------------------------------
+# per-joint softmax entropy
+# ------------------------------------------------------------------------------------------
+@pytest.mark.skipif(not ref_loader.available(), reason="/root/reference is not mounted here")
+def test_entropy_oracle_vs_live_reference_and_scipy():
+    from scipy import stats
+    from oracle import integral_np as O
+    Lm = ref_loader.load_loss_module()
+    hm = synth.heatmaps(2, 21, 6, 7, 8, "peaked", seed=4)
+    p = Lm.softmax_integral_tensor2(torch.as_tensor(hm).double(), 21, 8, 7, 6).numpy()
+    ref = np.array([[stats.entropy(p[b, j]) for j in range(21)] for b in range(2)])
+    assert np.abs(O.softmax_entropy(hm, 21, 6, 7, 8) - ref).max() < 1e-12
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("geom,regime,dtype", [((16, 16, 16), "peaked", "f32"), ((64, 64, 64), "sharp", "f32"),
+                                               ((5, 6, 7), "noise", "f32"), ((32, 32, 32), "peaked", "bf16")])
+def test_entropy_kernel_vs_oracle(geom, regime, dtype):
+    """Tolerance 1e-5 relative (+1e-6 nats): fp32 exponentials, fp64 accumulation."""
+    from nets import loss as L
+    from oracle import integral_np as O
+    D, H, W = geom
+    hm = synth.heatmaps(2, 21, D, H, W, regime, seed=8)
+    x = torch.as_tensor(hm).cuda()
+    if dtype == "bf16":
+        x = x.bfloat16()
+        hm = x.float().cpu().numpy()           # the oracle sees the rounded logits
+    ref = O.softmax_entropy(hm, 21, D, H, W)
+    got = L.softmax_entropy(x, 21, W, H, D).cpu().numpy()
+    assert got.shape == (2, 21)
+    assert (np.abs(got - ref) <= 1e-5 * np.abs(ref) + 1e-6).all(), np.abs(got - ref).max()
+    hm2 = hm.copy().reshape(2, 21, -1)
+    hm2[0, 0, :5] = -np.inf                    # -inf logits contribute 0, not NaN
+    y = torch.as_tensor(hm2.reshape(hm.shape)).cuda()
+    if dtype == "bf16":
+        y = y.bfloat16()
+    g2 = L.softmax_entropy(y, 21, W, H, D).cpu().numpy()
+    assert np.isfinite(g2).all() and abs(g2[0, 0] - O.softmax_entropy(hm2.reshape(hm.shape), 21, D, H, W)[0, 0]) < 1e-4
