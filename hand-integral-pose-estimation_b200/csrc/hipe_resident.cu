@@ -95,6 +95,8 @@ struct Params {
     double* partials;     // n_vol * P * 8 doubles
     unsigned* counters;   // n_vol
     unsigned* err;        // 1 word: set when a spin limit was hit
+    unsigned* ticket;     // 1 word: scalar warps that have finished (the last one sums the loss)
+    double* loss_out;     // nullable: norm * sum of loss_terms, written by the last scalar warp
 };
 
 struct Smem {
@@ -325,6 +327,22 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(&sm.scal_ready[item_no % kNB]));
+        }
+        // The loss scalar without a second launch: the scalar warps are the writers of loss_terms,
+        // so the last of them to finish sums the terms (fixed order: lane-strided partials, then
+        // the shuffle tree) -- loss.py:88-89.
+        if (p.loss_out && p.loss_terms) {
+            __threadfence();
+            unsigned t = 0;
+            if (lane == 0) t = atomicAdd(p.ticket, 1u);
+            t = __shfl_sync(0xffffffffu, t, 0);
+            if (t == gridDim.x - 1) {
+                __threadfence();
+                double acc = 0.0;
+                for (long long i = lane; i < p.n_vol * 3; i += 32) acc += __ldcg(p.loss_terms + i);
+                acc = warp_sum(acc);
+                if (lane == 0) p.loss_out[0] = acc * p.norm;
+            }
         }
         return;
     }
@@ -631,7 +649,7 @@ static bool pick_geom(int dtype, int D, int H, int W, Geom* g) {
 }
 
 static size_t ws_counters_bytes(long long n_vol) {
-    return (size_t)(((n_vol + 1) * sizeof(unsigned) + 255) / 256 * 256);   // counters + the error word
+    return (size_t)(((n_vol + 2) * sizeof(unsigned) + 255) / 256 * 256);   // counters + error word + ticket
 }
 
 }  // namespace res
@@ -650,12 +668,14 @@ extern "C" long long hipe_resident_workspace_bytes(int dtype, long long n_vol, i
 extern "C" int hipe_joint_loss_resident(const void* logits, int dtype, long long n_vol, int D, int H, int W,
                                         const void* gt, const void* vis, int tgt_dtype, double norm,
                                         float* coords, double* expect, float* stats, double* loss_terms,
-                                        void* dlogits, void* workspace, long long workspace_bytes, void* stream) {
+                                        double* loss, void* dlogits, void* workspace, long long workspace_bytes,
+                                        void* stream) {
     if (dtype != HIPE_F32 && dtype != HIPE_BF16) return HIPE_E_DTYPE;
     if (tgt_dtype != HIPE_F32 && tgt_dtype != HIPE_F64) return HIPE_E_DTYPE;
     if (n_vol < 0 || D <= 0 || H <= 0 || W <= 0) return HIPE_E_SHAPE;
     if (n_vol == 0) return 0;
     if (!logits || !gt || !vis || !dlogits || !workspace) return HIPE_E_NULL;
+    if (loss && !loss_terms) return HIPE_E_NULL;
     if ((reinterpret_cast<uintptr_t>(logits) & 15) || (reinterpret_cast<uintptr_t>(dlogits) & 15) ||
         (reinterpret_cast<uintptr_t>(workspace) & 255))
         return HIPE_E_ALIGN;
@@ -710,6 +730,8 @@ extern "C" int hipe_joint_loss_resident(const void* logits, int dtype, long long
     const size_t cb = res::ws_counters_bytes(n_vol);
     p.counters = static_cast<unsigned*>(workspace);
     p.err = p.counters + n_vol;
+    p.ticket = p.counters + n_vol + 1;
+    p.loss_out = loss;
     p.partials = reinterpret_cast<double*>(static_cast<unsigned char*>(workspace) + cb);
     if (grid > p.n_items) grid = p.n_items;
 

@@ -27,7 +27,7 @@ SIGNATURES = {
     "hipe_joint_loss_fused": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp,
                                    _i, _i, _vp]),
     "hipe_resident_workspace_bytes": (_ll, [_i, _ll, _i, _i, _i]),
-    "hipe_joint_loss_resident": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp,
+    "hipe_joint_loss_resident": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp, _vp,
                                       _vp, _ll, _vp]),
     "hipe_scale_inplace": (_i, [_vp, _i, _ll, _vp, _vp]),
     "hipe_scale_inplace_s": (_i, [_vp, _i, _ll, _vp, _i, _vp]),

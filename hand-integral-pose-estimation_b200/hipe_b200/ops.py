@@ -249,8 +249,10 @@ def resident_timed_out(device, n_vol):
     return bool(ws[4 * n_vol:4 * n_vol + 4].view(torch.int32).item() != 0)
 
 
-def joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm):
-    """hipe_joint_loss_resident: same outputs as joint_loss_fused, each volume read from HBM once."""
+def joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm, loss_out=None):
+    """hipe_joint_loss_resident: same outputs as joint_loss_fused, each volume read from HBM once.
+    `loss_out`: optional 0-dim fp64 CUDA tensor that receives norm * sum(loss terms) from the same
+    launch (the last CTA to finish sums them)."""
     _need_cuda(logits, "heatmaps")
     code = _logits_code(logits)
     if not logits.is_contiguous():
@@ -274,19 +276,21 @@ def joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm):
         with _launch("joint_loss_resident", logits):
             check(lib.hipe_joint_loss_resident(
                 logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
-                coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), dlogits.data_ptr(),
-                ws.data_ptr(), ws.numel(), _stream(logits)))
+                coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), _ptr(loss_out),
+                dlogits.data_ptr(), ws.data_ptr(), ws.numel(), _stream(logits)))
     return coords, expect, stats, terms, dlogits
 
 
-def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, variant=None, mode=None):
-    """One launch: coords, expect, stats, per-coordinate loss terms (n_vol*3 fp64), dlogits."""
+def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, variant=None, mode=None, loss_out=None):
+    """One launch: coords, expect, stats, per-coordinate loss terms (n_vol*3 fp64), dlogits.
+    `loss_out` (0-dim fp64 CUDA tensor, optional) is filled with the loss scalar: by the resident
+    launch itself, else by hipe_sum_f64."""
     _need_cuda(logits, "heatmaps")
     mode = FUSED_MODE if mode is None else mode
     if mode == "resident" or (mode == "auto" and cluster is None and variant is None
                               and fused_plan(logits, n_vol, D, H, W) == "resident"):
         try:
-            return joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm)
+            return joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm, loss_out)
         except _lib.HipeError as e:
             if mode == "resident" or "error %d:" % _lib.E_UNSUPPORTED not in str(e):
                 raise
@@ -308,6 +312,10 @@ def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, varian
             coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), dlogits.data_ptr(),
             DEFAULT_CLUSTER if cluster is None else cluster,
             DEFAULT_VARIANT if variant is None else variant, _stream(logits)))
+    if loss_out is not None:
+        with _on(dev), _launch("sum_f64", terms):
+            check(_lib.load().hipe_sum_f64(terms.data_ptr(), terms.numel(), float(norm), loss_out.data_ptr(),
+                                           _stream(terms)))
     return coords, expect, stats, terms, dlogits
 
 
@@ -480,12 +488,11 @@ class FusedJointLossFunction(torch.autograd.Function):
         exchange kernel instead of a separate launch."""
         B = heatmap_out.shape[0]
         n_vol = B * num_joints
-        coords, _, _, terms, dlogits = joint_loss_fused(heatmap_out, n_vol, D, H, W, gt, vis, norm)
         out_dtype = torch.promote_types(torch.float32, torch.promote_types(gt.dtype, vis.dtype))
-        if reduce_loss:
-            loss = sum_f64(terms, norm).to(out_dtype)
-        else:
-            loss = torch.empty((), dtype=out_dtype, device=terms.device)
+        loss64 = torch.empty((), dtype=torch.float64, device=heatmap_out.device)
+        coords, _, _, terms, dlogits = joint_loss_fused(heatmap_out, n_vol, D, H, W, gt, vis, norm,
+                                                        loss_out=loss64 if reduce_loss else None)
+        loss = loss64.to(out_dtype)
         ctx.save_for_backward(dlogits)
         ctx.in_shape = heatmap_out.shape
         ctx.mark_non_differentiable(coords, terms)

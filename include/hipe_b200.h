@@ -146,8 +146,10 @@ HIPE_API long long hipe_resident_workspace_bytes(int dtype, long long n_vol, int
 HIPE_API int hipe_joint_loss_resident(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
                              const void* gt_dev, const void* vis_dev, int tgt_dtype, double norm,
                              float* coords_dev, double* expect_dev, float* stats_dev,
-                             double* loss_terms_dev /* n_vol*3 */, void* dlogits_dev,
-                             void* workspace_dev, long long workspace_bytes, void* stream);
+                             double* loss_terms_dev /* n_vol*3 */,
+                             double* loss_dev /* nullable: norm * sum(loss_terms), by the last CTA */,
+                             void* dlogits_dev, void* workspace_dev, long long workspace_bytes,
+                             void* stream);
 
 /*
  * x[i] *= *gscale_dev for n elements of `dtype`, in place; returns without touching memory when

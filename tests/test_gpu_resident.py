@@ -196,3 +196,33 @@ def test_default_module_picks_the_measured_fastest_launch():
     assert abs(loss.item() - l2.item()) <= 1e-6 * abs(l2.item())   # two kernels, fp32 coordinates
     scale = y.grad.view(16 * 21, -1).abs().amax(dim=1, keepdim=True)
     assert ((x.grad - y.grad).view(16 * 21, -1).abs() <= 2e-5 * scale + 1e-12).all()
+
+
+def test_resident_launch_writes_the_loss_scalar_itself():
+    """loss_dev of hipe_joint_loss_resident: the last CTA's fixed-order sum of the loss terms equals
+    hipe_sum_f64 of the same terms to fp64 round-off, repeats bit-identically, and the module's
+    step needs no separate reduction launch."""
+    from hipe_b200 import ops
+    from nets import loss as L
+    D = H = W = 64
+    J, B = 21, 16
+    hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=13)
+    gt, vis = synth.targets(B, J, seed=13, zero_vis_frac=0.1)
+    x = _cuda(hm)
+    vals = []
+    for _ in range(3):
+        out = torch.full((), float("nan"), dtype=torch.float64, device="cuda")
+        c, e, s, terms, d = ops.joint_loss_resident(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B, loss_out=out)
+        ref = ops.sum_f64(terms, 1.0 / B)
+        assert abs(out.item() - ref.item()) <= 1e-14 * abs(ref.item())
+        vals.append(out.item())
+    assert vals[0] == vals[1] == vals[2]
+    ref_loss = O.joint_location_loss(hm.astype(np.float64), gt, vis)
+    assert abs(vals[0] - ref_loss) <= 1e-5 * abs(ref_loss)
+    ops.KERNEL_EVENTS = {}
+    try:
+        xg = _cuda(hm).requires_grad_(True)
+        L.JointLocationLoss()(xg, _cuda(gt), _cuda(vis)).backward()
+        assert "joint_loss_resident" in ops.KERNEL_EVENTS and "sum_f64" not in ops.KERNEL_EVENTS
+    finally:
+        ops.KERNEL_EVENTS = None
