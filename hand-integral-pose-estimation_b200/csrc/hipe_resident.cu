@@ -49,8 +49,14 @@ namespace res {
 
 constexpr int kC = 256;               // threads per team
 constexpr int kNW = kC / 32;          // warps per team
-constexpr int kRSlots = 7;            // reduce ring depth (HBM latency to cover)
-constexpr int kWSlots = 6;            // write ring depth (L2 latency to cover)
+#ifndef HIPE_RES_RSLOTS
+#define HIPE_RES_RSLOTS 7
+#endif
+#ifndef HIPE_RES_WSLOTS
+#define HIPE_RES_WSLOTS 6
+#endif
+constexpr int kRSlots = HIPE_RES_RSLOTS;   // reduce ring depth (HBM latency to cover)
+constexpr int kWSlots = HIPE_RES_WSLOTS;   // write ring depth (L2 latency to cover)
 constexpr int kSlotBytes = 16384;     // ring slot
 constexpr int kKP = 4;                // 16-byte vectors per thread per stage
 constexpr int kMaxItemStages = 16;    // unroll bound: an item never exceeds 16 stages (256 KB)
