@@ -72,6 +72,26 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// Release of a ring slot by a consumer: an arrive that cannot ISSUE before the shared-memory loads
+// that produced `dep` have returned.  A plain `ld.shared ...; mbarrier.arrive` pair is ordered in
+// program order only: the arrive does not consume the loaded registers, so it can complete while
+// the loads still sit in the MIO queue, the producer then refills the slot by TMA, and the loads
+// return the NEXT stage's bytes.  Seen on B200 in the persistent kernel's tail under concurrent
+// streams (scripts/diag_threads.py: one warp-visit of 512 bytes computed from the logits of the
+// stage six slots later).  `dep` must be derived from one register of EVERY load instruction of
+// the stage (the scoreboard is per instruction); both predicated forms arrive, so exactly one
+// arrive happens whatever the data.
+__device__ __forceinline__ void mbar_arrive_after_loads(uint32_t bar, uint32_t dep) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.u32 p, %1, 0x9e3779b9;\n"
+        "@p mbarrier.arrive.shared::cta.b64 _, [%0];\n"
+        "@!p mbarrier.arrive.shared::cta.b64 _, [%0];\n"
+        "}\n" ::"r"(bar),
+        "r"(dep)
+        : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n"

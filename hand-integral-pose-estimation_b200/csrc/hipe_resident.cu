@@ -49,6 +49,14 @@ namespace res {
 
 constexpr int kC = 256;               // threads per team
 constexpr int kNW = kC / 32;          // warps per team
+// When a consumer warp hands a ring slot back relative to the arithmetic of the previous stage:
+// 0 = right after issuing the loads (the arrive then waits for them: no overlap of two stages'
+// dependency chains), 1 = half-way through the previous stage's arithmetic, 2 = after it.
+// Measured (scripts/ab_resident_release.sh, fp32 64^3 x 1344): 0 -> 0.519 ms, 1 -> 0.568, 2 -> 0.572:
+// the launch is far more sensitive to WHEN a slot comes back than to how many there are.
+#ifndef HIPE_RES_RELEASE
+#define HIPE_RES_RELEASE 0
+#endif
 #ifndef HIPE_RES_RSLOTS
 #define HIPE_RES_RSLOTS 7
 #endif
@@ -428,14 +436,25 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
 #pragma unroll
                     for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * p.pass_bytes);
                 }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(&sm.rempty[slot]));
+            };
+            // The slot goes back to the producer only once the loads have RETURNED (the arrive
+            // consumes a word of every load instruction; a warp's scoreboard covers all its
+            // lanes), and one compute phase later, so that waiting for them stalls nothing.
+            auto release = [&](unsigned gg, const uint4 (&src)[kKP]) {
+                uint32_t dep = 0;
+#pragma unroll
+                for (int q = 0; q < kKP; ++q) dep ^= src[q].x;
+                if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.rempty[gg % kRSlots]), active ? dep : 0u);
             };
             fetch(g, raw[0]);
+            release(g, raw[0]);
 #pragma unroll
             for (int s = 0; s < kMaxItemStages; ++s) {
                 if (s >= it.n) break;
-                if (s + 1 < it.n) fetch(g + s + 1, raw[(s + 1) & 1]);
+                if (s + 1 < it.n) {
+                    fetch(g + s + 1, raw[(s + 1) & 1]);
+                    if (HIPE_RES_RELEASE == 0) release(g + s + 1, raw[(s + 1) & 1]);
+                }
                 if (active) {
                     float v[kKP][VEC];
 #pragma unroll
@@ -467,6 +486,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                     float rowsum[kKP];
 #pragma unroll
                     for (int q = 0; q < kKP; ++q) {
+                        if (HIPE_RES_RELEASE == 1 && q == kKP / 2 && s + 1 < it.n) release(g + s + 1, raw[(s + 1) & 1]);
                         float2 e2[VEC / 2];
 #pragma unroll
                         for (int j = 0; j < VEC / 2; ++j) {
@@ -484,6 +504,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                     syb = fma((double)yb, dt, syb);
                     szb = fma((double)zb, dt, szb);
                 }
+                if (HIPE_RES_RELEASE == 2 && s + 1 < it.n) release(g + s + 1, raw[(s + 1) & 1]);
                 // next stage's base row (uniform): SR | H or H | SR, so one of the two moves
                 yb += p.SR;
                 while (yb >= p.H) { yb -= p.H; ++zb; }
@@ -578,17 +599,26 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
 #pragma unroll
                 for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * p.pass_bytes);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&sm.wempty[slot]));
+        };
+        auto release = [&](unsigned gg, const uint4 (&src)[kKP]) {   // see the reduce team
+            uint32_t dep = 0;
+#pragma unroll
+            for (int q = 0; q < kKP; ++q) dep ^= src[q].x;
+            if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.wempty[gg % kWSlots]), active ? dep : 0u);
         };
         fetch(g, raw[0]);
+        release(g, raw[0]);
 #pragma unroll
         for (int s = 0; s < kMaxItemStages; ++s) {
             if (s >= it.n) break;
-            if (s + 1 < it.n) fetch(g + s + 1, raw[(s + 1) & 1]);
+            if (s + 1 < it.n) {
+                    fetch(g + s + 1, raw[(s + 1) & 1]);
+                    if (HIPE_RES_RELEASE == 0) release(g + s + 1, raw[(s + 1) & 1]);
+                }
             if (active) {
 #pragma unroll
                 for (int q = 0; q < kKP; ++q) {
+                    if (HIPE_RES_RELEASE == 1 && q == kKP / 2 && s + 1 < it.n) release(g + s + 1, raw[(s + 1) & 1]);
                     const float rtv = rt[s * p.SR + rr + q * p.R];
                     float v[VEC], o[VEC];
                     V16::unpack(raw[s & 1][q], v);
@@ -604,6 +634,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                     stg_stream(gdst + (long long)s * p.stage_bytes + q * p.pass_bytes, V16::pack(o));
                 }
             }
+            if (HIPE_RES_RELEASE == 2 && s + 1 < it.n) release(g + s + 1, raw[(s + 1) & 1]);
         }
         g += it.n;
         // progress report for the reduce producer's L2-window throttle

@@ -185,8 +185,15 @@ __device__ __forceinline__ void reduce_pass(const Params& p, const Tile& t, unsi
             }
         }
         if constexpr (kTma) {
-            __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&sm.empty[it % kStages]));
+            // hand the slot back only once the loads of this stage have returned
+            // (mbar_arrive_after_loads: the arrive consumes a word of every load instruction; a
+            // warp's scoreboard covers all its lanes)
+            uint32_t dep = 0;
+#pragma unroll
+            for (int q = 0; q < KP; ++q)
+#pragma unroll
+                for (int h = 0; h < NV; ++h) dep ^= __float_as_uint(v[q][h * VEC]);
+            if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.empty[it % kStages]), dep);
         }
         // ---- online max ----
         if constexpr (kSoftmax) {
@@ -402,8 +409,11 @@ __device__ __forceinline__ void write_pass(const Params& p, const Tile& t, unsig
         }
         if constexpr (kTma) {
             if (!resident) {
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(&sm.empty[it % kStages]));
+                uint32_t dep = 0;
+#pragma unroll
+                for (int q = 0; q < kPasses; ++q)
+                    if (whole || i * kPasses + q < nvis) dep ^= __float_as_uint(v[q][0]);
+                if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.empty[it % kStages]), dep);
             }
         }
 #pragma unroll
