@@ -239,14 +239,17 @@ static int check_device() {
     return major == 10 ? 0 : HIPE_E_ARCH;
 }
 
-static int pick_cluster(int op, long long n_vol, long long vol_bytes, int NR) {
+static int pick_cluster(int op, long long n_vol, long long vol_bytes, int NR, int esz) {
     // Write-only and fused launches: aim for >= ~8 waves of 3 resident CTAs over 148 SMs while
     // keeping every CTA's share >= 64 KB (finer grain = shorter tail; no reduction to pay for).
     // Reduce-only launches pay a cluster barrier + DSMEM merge per CTA, so they split a volume
     // only when there are too few volumes to fill the machine twice over (measured on B200:
     // 1344 x 1 MiB volumes run 0.236 ms at S=1, 0.291 ms at S=4).
     const bool reduce_only = (op == OP_REDUCE_SOFTMAX || op == OP_REDUCE_PLAIN);
-    const long long want = reduce_only ? 148ll * 6 : 148ll * 24;
+    // Fused launches on 2-byte logits want half the split (bf16 64^3 x 2688 volumes: 0.635 ms at
+    // S=1, 0.679 at S=2, 0.813 at S=4; x 1344: 0.336 / 0.355 / 0.414; 56^3 x 4032: 0.641 at S=1,
+    // 0.768 at S=2; 96^3 x 672: 0.615 / 0.592 / 0.600).
+    const long long want = reduce_only ? 148ll * 6 : (op == OP_FUSED && esz == 2) ? 148ll * 6 : 148ll * 24;
     const long long min_share = reduce_only ? 131072 : 65536;
     int S = 1;
     while (S < kMaxCluster && n_vol * S < want && vol_bytes / (2 * S) >= min_share && NR / (2 * S) >= 1) S *= 2;
@@ -311,7 +314,7 @@ static int dispatch(Params p, int cluster, int variant, cudaStream_t st) {
     }
     p.G = (int)(row_b / 16);
     p.R = kConsumers / p.G;
-    int S = cluster ? cluster : pick_cluster(kOp, p.n_vol, p.vol_bytes, p.NR);
+    int S = cluster ? cluster : pick_cluster(kOp, p.n_vol, p.vol_bytes, p.NR, esz);
     const bool tma_ = (variant == HIPE_VARIANT_AUTO) ? true : (variant == HIPE_VARIANT_TMA);
     const long long ring_rows = (long long)kStages * kPasses * p.R;   // rows one CTA's ring holds
     if (kOp == OP_FUSED && tma_ && !cluster && getenv("HIPE_RESIDENT")) {

@@ -213,16 +213,23 @@ def _fused_plan(logits, n_vol, D, H, W):
     """Which launch computes loss + gradient fastest for this geometry, from B200 measurements
     (profiles/r1_configs.md): "resident" (persistent on-chip launch, one HBM read + one write)
     for the fp32 geometry it is tuned for -- 256-byte rows, volumes <= 1 MiB, i.e. 21x64^3;
-    "stream" (one launch, second read from L2) for other fp32 volumes; None = the two-launch
-    forward + recompute backward (bf16: the fused launches gain < 4 % or lose)."""
+    "stream" (one launch, second read from L2) for other fp32 volumes >= 512 KiB and for bf16
+    volumes >= 256 KiB (bf16 64^3 x 2688: 0.635 ms vs 0.701 for the pair; 56^3 x 4032: 0.641 vs
+    0.715; 96^3 x 672: 0.592 vs 0.642; equal at 10752 volumes); None = the two-launch forward +
+    recompute backward."""
+    esz = logits.element_size()
+    vol_bytes = D * H * W * esz
+    if logits.dtype == torch.bfloat16:
+        return "stream" if (W * esz) % 16 == 0 and vol_bytes >= (1 << 18) else None
     if logits.dtype != torch.float32:
         return None
-    vol_bytes = D * H * W * 4
     if W * 4 == 256 and vol_bytes <= (1 << 20) and n_vol >= 296 and resident_supported(logits, n_vol, D, H, W):
         return "resident"
     if (W * 4) % 16 == 0 and vol_bytes >= (1 << 19):
         return "stream"
     return None
+
+
 _WORKSPACES = {}             # (device index, stream) -> uint8 scratch tensor, grown on demand
 
 

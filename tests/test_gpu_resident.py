@@ -169,13 +169,14 @@ def test_module_uses_resident_launch_and_scales_upstream_gradient():
 
 def test_default_module_picks_the_measured_fastest_launch():
     """fused=None: 21x64^3 fp32 batches go to the resident launch, other fp32 volumes >= 512 KB to
-    the streaming fused launch, bf16 and small volumes to forward + recompute backward."""
+    the streaming fused launch (bf16: >= 256 KB), small volumes to forward + recompute backward."""
     from hipe_b200 import ops
     from nets import loss as L
     x64 = torch.empty((16, 21 * 64, 64, 64), device="cuda")
     assert ops.fused_plan(x64, 16 * 21, 64, 64, 64) == "resident"
     assert ops.fused_plan(x64[:2], 42, 64, 64, 64) == "stream"           # too few volumes to fill the grid
-    assert ops.fused_plan(x64.bfloat16(), 16 * 21, 64, 64, 64) is None
+    assert ops.fused_plan(x64.bfloat16(), 16 * 21, 64, 64, 64) == "stream"
+    assert ops.fused_plan(x64.bfloat16()[:, :21 * 32, :32, :32], 16 * 21, 32, 32, 32) is None
     x56 = torch.empty((2, 21 * 56, 56, 56), device="cuda")
     assert ops.fused_plan(x56, 42, 56, 56, 56) == "stream"
     x16 = torch.empty((2, 21 * 16, 16, 16), device="cuda")
