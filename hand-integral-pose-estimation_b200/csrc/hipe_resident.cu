@@ -34,6 +34,13 @@
 // items; write teams wait on volumes whose partials come from reduce teams: no cycle, provided
 // all CTAs are co-resident.
 //
+// Tried and dropped: CLAIMING items from a global counter instead of dealing them round-robin
+// (so that an SM with less bandwidth takes fewer).  The claim has to come after the lag
+// throttle to stay deadlock-free, which puts an atomic round trip on the one path the launch
+// is sensitive to: 0.69 ms against 0.57 ms for the round-robin in the same build.  The L2
+// policies of the two rings and of the gradient stores were swept too (evict_last / normal /
+// evict_first x lag 3-5): nothing beats evict_last reads + evict_first re-reads + plain stores.
+//
 // Precision (same contract as hipe_stream_kernel.cuh): exponentials are fp32; each expectation
 // is a ratio of fp64 sums built from the SAME rounded fp32 atoms, so rounding only re-weights
 // voxels.  Two families of atoms are used, each with its own denominator:
@@ -77,6 +84,7 @@ constexpr int kNB = 8;                // scalar records in flight (scalar warp -
 constexpr int kPB = 4;                // per-item warp partials in flight (reduce team -> publish warp)
 constexpr int kThreads = 2 * kC + 128; // two teams + two producer warps + the scalar warp + the publish warp
 constexpr unsigned kSpinLimit = 1u << 22;
+constexpr int kProfN = 20;                // wait classes of the diagnostic profile (HIPE_RES_PROF)
 constexpr float kLazy = 16.f;         // lazy re-basing threshold of the online softmax (natural-log units)
 
 struct Params {
@@ -129,6 +137,10 @@ struct Smem {
         float M;                  // volume maximum
         float pad;
     } scal[kNB];
+#ifdef HIPE_RES_PROF
+    unsigned long long prof[kProfN];
+    unsigned prof_done;
+#endif
 };
 
 struct Item {
@@ -176,6 +188,39 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
     return v;
 }
 
+// Wait-time profile (diagnostic builds only, -DHIPE_RES_PROF; scripts/diag_resident_waits.sh):
+// lane 0 of every warp adds the clock cycles it spent in each class of wait to a shared-memory
+// table; the last warp of the CTA to finish adds the table to g_prof.
+#ifdef HIPE_RES_PROF
+__device__ unsigned long long g_prof[kProfN];
+#define RES_PROF_T0() const long long prof_t0_ = clock64()
+#define RES_PROF_ADD(cls)                                                                              \
+    do {                                                                                               \
+        if ((threadIdx.x & 31) == 0) atomicAdd(&sm.prof[cls], (unsigned long long)(clock64() - prof_t0_)); \
+    } while (0)
+#define RES_WAIT(cls, bar, par)          \
+    do {                                 \
+        RES_PROF_T0();                   \
+        mbar_wait_bounded(bar, par);     \
+        RES_PROF_ADD(cls);               \
+    } while (0)
+#define RES_FINISH(cls)                                                                      \
+    do {                                                                                     \
+        __syncwarp();                                                                        \
+        if ((threadIdx.x & 31) == 0) {                                                       \
+            atomicAdd(&sm.prof[cls], (unsigned long long)(clock64() - prof_start_));         \
+            __threadfence_block();                                                           \
+            if (atomicAdd(&sm.prof_done, 1u) == kThreads / 32 - 1) {                         \
+                __threadfence_block();                                                       \
+                for (int k_ = 0; k_ < kProfN; ++k_) atomicAdd(&g_prof[k_], sm.prof[k_]);     \
+            }                                                                                \
+        }                                                                                    \
+    } while (0)
+#else
+#define RES_WAIT(cls, bar, par) mbar_wait_bounded(bar, par)
+#define RES_FINISH(cls) do { } while (0)
+#endif
+
 __device__ __forceinline__ float rebase_w(float m_from, float m_to) {
     // 2^(fl(m_from*log2e) - fl(m_to*log2e)): the same rounded products the exponentials used
     return (m_from == kNegInf) ? 0.f : ex2(__fsub_rn(__fmul_rn(m_from, kLog2e), __fmul_rn(m_to, kLog2e)));
@@ -219,8 +264,15 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
         }
         mbar_fence_init();
         fence_proxy_async();
+#ifdef HIPE_RES_PROF
+        for (int k = 0; k < kProfN; ++k) sm.prof[k] = 0;
+        sm.prof_done = 0;
+#endif
     }
     __syncthreads();
+#ifdef HIPE_RES_PROF
+    const long long prof_start_ = clock64();
+#endif
 
     if (threadIdx.x >= 2 * kC + 96) {
         // ------------------------------- publish warp -------------------------------
@@ -231,7 +283,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
         for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
             const Item it = decode(p, w);
             const unsigned sb = item_no % kPB;
-            mbar_wait_bounded(smem_u32(&sm.red_ready[sb]), (item_no / kPB) & 1);
+            RES_WAIT(15, smem_u32(&sm.red_ready[sb]), (item_no / kPB) & 1);
             const float pm = (lane < kNW) ? sm.wmax[sb][lane] : kNegInf;
             double a[kNSums];
 #pragma unroll
@@ -257,6 +309,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                 atomicAdd(p.counters + it.vol, 1u);
             }
         }
+        RES_FINISH(16);
         return;
     }
 
@@ -271,7 +324,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
             const Item it = decode(p, w);
             if (item_no >= (unsigned)kNB) {
                 const unsigned d = item_no - (unsigned)kNB;   // its record slot must have been consumed
-                mbar_wait_bounded(smem_u32(&sm.w_done[d % kRD]), (d / kRD) & 1);
+                RES_WAIT(9, smem_u32(&sm.w_done[d % kRD]), (d / kRD) & 1);
             }
             Smem::Scal& rec = sm.scal[item_no % kNB];
             // targets first: their latency overlaps the flag wait
@@ -283,6 +336,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                                : (double)reinterpret_cast<const float*>(p.vis)[it.vol * 3 + lane];
             }
             unsigned spins = 0;
+#ifdef HIPE_RES_PROF
+            RES_PROF_T0();
+#endif
             while (ld_acquire_u32(p.counters + it.vol) < (unsigned)p.P) {
                 __nanosleep(64);
                 if (++spins > kSpinLimit) {
@@ -290,6 +346,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                     break;
                 }
             }
+#ifdef HIPE_RES_PROF
+            RES_PROF_ADD(6);
+#endif
             float mi = kNegInf;
             double a[kNSums];
     #pragma unroll
@@ -358,6 +417,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                 if (lane == 0) p.loss_out[0] = acc * p.norm;
             }
         }
+        RES_FINISH(14);
         return;
     }
 
@@ -376,12 +436,15 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                 // L2 window: the reduce side stays at most `lag` items ahead of the write side
                 if (!for_write && item_no >= (unsigned)p.lag) {
                     const unsigned d = item_no - (unsigned)p.lag;
-                    mbar_wait_bounded(smem_u32(&sm.w_done[d % kRD]), (d / kRD) & 1);
+                    RES_WAIT(4, smem_u32(&sm.w_done[d % kRD]), (d / kRD) & 1);
                 }
                 const unsigned char* src = p.in + it.vol * p.vol_bytes + (long long)it.sv0 * p.stage_bytes;
                 for (int s = 0; s < it.n; ++s, ++g) {
                     const unsigned slot = g % nslots;
-                    if (g >= (unsigned)nslots) mbar_wait_bounded(smem_u32(&empty[slot]), ((g / nslots) - 1) & 1);
+                    if (g >= (unsigned)nslots) {
+                        if (for_write) RES_WAIT(3, smem_u32(&empty[slot]), ((g / nslots) - 1) & 1);
+                        else RES_WAIT(2, smem_u32(&empty[slot]), ((g / nslots) - 1) & 1);
+                    }
                     const uint32_t bar = smem_u32(&full[slot]);
                     mbar_arrive_expect_tx(bar, (uint32_t)p.stage_bytes);
                     tma_load_1d(ring + slot * kSlotBytes, src + (long long)s * p.stage_bytes, (uint32_t)p.stage_bytes,
@@ -389,6 +452,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                 }
             }
         }
+        RES_FINISH(threadIdx.x >= 2 * kC + 32 ? 13 : 12);
         return;
     }
 
@@ -430,7 +494,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
             uint4 raw[2][kKP];
             auto fetch = [&](unsigned gg, uint4 (&dst)[kKP]) {
                 const unsigned slot = gg % kRSlots;
-                mbar_wait_bounded(smem_u32(&sm.rfull[slot]), (gg / kRSlots) & 1);
+                RES_WAIT(0, smem_u32(&sm.rfull[slot]), (gg / kRSlots) & 1);
                 if (active) {
                     const uint32_t sbase = lds_base + slot * kSlotBytes;
 #pragma unroll
@@ -549,7 +613,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
             for (int k = 0; k < kNSums; ++k) q7[k] = warp_sum(q7[k] * f);
             // hand the warp's partial to the publish warp: no team barrier, nobody waits for the
             // global round trip
-            if (item_no >= (unsigned)kPB) mbar_wait_bounded(smem_u32(&sm.red_free[sb]), ((item_no / kPB) - 1) & 1);
+            if (item_no >= (unsigned)kPB) RES_WAIT(7, smem_u32(&sm.red_free[sb]), ((item_no / kPB) - 1) & 1);
             if (lane == 0) {
 #pragma unroll
                 for (int k = 0; k < kNSums; ++k) sm.wred[sb][warp][k] = q7[k];
@@ -557,6 +621,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                 mbar_arrive(smem_u32(&sm.red_ready[sb]));
             }
         }
+        RES_FINISH(10);
         return;
     }
 
@@ -566,7 +631,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
     unsigned item_no = 0;
     for (long long w = blockIdx.x; w < p.n_items; w += gridDim.x, ++item_no) {
         const Item it = decode(p, w);
-        mbar_wait_bounded(smem_u32(&sm.scal_ready[item_no % kNB]), (item_no / kNB) & 1);
+        RES_WAIT(5, smem_u32(&sm.scal_ready[item_no % kNB]), (item_no / kNB) & 1);
         const Smem::Scal& rec = sm.scal[item_no % kNB];
         float* rt = sm.rt[item_no & 1];
         const double kxd = rec.K[0], kyd = rec.K[1], kzd = rec.K[2];
@@ -587,13 +652,22 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                 rt[lr] = (float)(kyd * ((double)y - Ey) + kzd * ((double)z - Ez));
             }
         }
-        team_barrier<2>();   // rt[b] visible; rt[1-b] is refilled only after every warp has passed here
+        // rt[b] visible; rt[1-b] is refilled only after every warp has passed here
+#ifdef HIPE_RES_PROF
+        {
+            RES_PROF_T0();
+            team_barrier<2>();
+            RES_PROF_ADD(8);
+        }
+#else
+        team_barrier<2>();
+#endif
 
         unsigned char* gdst = p.out + it.vol * p.vol_bytes + (long long)it.sv0 * p.stage_bytes + 16ll * tid;
         uint4 raw[2][kKP];
         auto fetch = [&](unsigned gg, uint4 (&dst)[kKP]) {
             const unsigned slot = gg % kWSlots;
-            mbar_wait_bounded(smem_u32(&sm.wfull[slot]), (gg / kWSlots) & 1);
+            RES_WAIT(1, smem_u32(&sm.wfull[slot]), (gg / kWSlots) & 1);
             if (active) {
                 const uint32_t sbase = lds_base + slot * kSlotBytes;
 #pragma unroll
@@ -641,6 +715,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&sm.w_done[item_no % kRD]));
     }
+    RES_FINISH(11);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -693,6 +768,19 @@ static size_t ws_counters_bytes(long long n_vol) {
 }  // namespace hipe
 
 using namespace hipe;
+
+#ifdef HIPE_RES_PROF
+// diagnostic builds only: read (and optionally clear) the wait-time table
+extern "C" __attribute__((visibility("default"))) int hipe_resident_prof(unsigned long long* out, int reset) {
+    cudaError_t e = cudaMemcpyFromSymbol(out, res::g_prof, sizeof(unsigned long long) * res::kProfN);
+    if (e != cudaSuccess) return (int)e;
+    if (reset) {
+        unsigned long long z[res::kProfN] = {};
+        e = cudaMemcpyToSymbol(res::g_prof, z, sizeof(z));
+    }
+    return (int)e;
+}
+#endif
 
 extern "C" long long hipe_resident_workspace_bytes(int dtype, long long n_vol, int D, int H, int W) {
     if (dtype != HIPE_F32 && dtype != HIPE_BF16) return 0;
