@@ -64,6 +64,19 @@ constexpr int kNW = kC / 32;          // warps per team
 #ifndef HIPE_RES_RELEASE
 #define HIPE_RES_RELEASE 0
 #endif
+// How a volume's P partials travel between CTAs.  0: data, __threadfence, arrival counter, then
+// the scalar warps read the data.  1: every 8-byte word of a partial validates itself (the
+// workspace is preset to all-ones, which no stored word can equal), so the publish warp needs no
+// fence + counter and the scalar warps poll the data itself: one global round trip instead of
+// three.  Parity-green, but NOT faster (scripts/ab_resident_partials.sh, same box: 0.543 ms vs
+// 0.549-0.551, the difference being the larger workspace preset), which says the publish -> merge
+// latency is not what paces the launch.  Kept as a build option.
+#ifndef HIPE_RES_SELFVALID
+#define HIPE_RES_SELFVALID 0
+#endif
+#ifndef HIPE_RES_POLL_NS
+#define HIPE_RES_POLL_NS 0
+#endif
 #ifndef HIPE_RES_RSLOTS
 #define HIPE_RES_RSLOTS 7
 #endif
@@ -221,6 +234,13 @@ __device__ unsigned long long g_prof[kProfN];
 #define RES_FINISH(cls) do { } while (0)
 #endif
 
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const void* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+constexpr unsigned long long kUnset = ~0ull;   // what cudaMemsetAsync(0xFF) leaves in a word
+
 __device__ __forceinline__ float rebase_w(float m_from, float m_to) {
     // 2^(fl(m_from*log2e) - fl(m_to*log2e)): the same rounded products the exponentials used
     return (m_from == kNegInf) ? 0.f : ex2(__fsub_rn(__fmul_rn(m_from, kLog2e), __fmul_rn(m_to, kLog2e)));
@@ -300,6 +320,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
 #pragma unroll
                 for (int o = kNW / 2; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
             }
+#if HIPE_RES_SELFVALID
+            if (lane < 8) {   // the xor tree leaves the sums in every lane of the first group
+                double mine = (double)cm;
+#pragma unroll
+                for (int k = 0; k < kNSums; ++k) mine = (lane == k) ? a[k] : mine;
+                unsigned long long bits = (unsigned long long)__double_as_longlong(mine);
+                if (bits == kUnset) bits = 0x7ff8000000000000ull;   // a NaN stays a NaN
+                __stcg(reinterpret_cast<unsigned long long*>(p.partials + (it.vol * p.P + it.i) * 8) + lane, bits);
+            }
+#else
             if (lane == 0) {
                 double* dst = p.partials + (it.vol * p.P + it.i) * 8;
 #pragma unroll
@@ -308,6 +338,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                 __threadfence();
                 atomicAdd(p.counters + it.vol, 1u);
             }
+#endif
         }
         RES_FINISH(16);
         return;
@@ -339,6 +370,49 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
 #ifdef HIPE_RES_PROF
             RES_PROF_T0();
 #endif
+            float mi = kNegInf;
+            double a[kNSums];
+#pragma unroll
+            for (int k = 0; k < kNSums; ++k) a[k] = 0.0;
+#if HIPE_RES_SELFVALID
+            // Poll the partials themselves: lane i keeps partial i's eight words once all of them
+            // are set; partials beyond 32 (P > 32: 96^3) are only checked here and read below.
+            unsigned long long bw[8];
+            for (;;) {
+                bool ok = true;
+                if (lane < p.P) {
+                    const double* src = p.partials + (it.vol * p.P + lane) * 8;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) bw[k] = ld_relaxed_u64(src + k);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) ok = ok && (bw[k] != kUnset);
+                }
+                for (int i = lane + 32; i < p.P; i += 32) {
+                    const double* src = p.partials + (it.vol * p.P + i) * 8;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) ok = ok && (ld_relaxed_u64(src + k) != kUnset);
+                }
+                if (__all_sync(0xffffffffu, ok)) break;
+                if (HIPE_RES_POLL_NS > 0) __nanosleep(HIPE_RES_POLL_NS);
+                if (++spins > kSpinLimit) {
+                    if (lane == 0) atomicExch(p.err, 1u);
+                    break;
+                }
+            }
+#ifdef HIPE_RES_PROF
+            RES_PROF_ADD(6);
+#endif
+            for (int i = lane; i < p.P; i += 32) {
+                double b[8];
+                if (i < 32) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) b[k] = __longlong_as_double((long long)bw[k]);
+                } else {
+                    const double* src = p.partials + (it.vol * p.P + i) * 8;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) b[k] = __longlong_as_double((long long)ld_relaxed_u64(src + k));
+                }
+#else
             while (ld_acquire_u32(p.counters + it.vol) < (unsigned)p.P) {
                 __nanosleep(64);
                 if (++spins > kSpinLimit) {
@@ -349,15 +423,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
 #ifdef HIPE_RES_PROF
             RES_PROF_ADD(6);
 #endif
-            float mi = kNegInf;
-            double a[kNSums];
-    #pragma unroll
-            for (int k = 0; k < kNSums; ++k) a[k] = 0.0;
             for (int i = lane; i < p.P; i += 32) {
                 const double* src = p.partials + (it.vol * p.P + i) * 8;
                 double b[8];
     #pragma unroll
                 for (int k = 0; k < 8; ++k) b[k] = __ldcg(src + k);
+#endif
                 const float pm = (float)b[7];
                 if (pm > mi) {
                     const double fr = (double)rebase_w(mi, pm);
@@ -407,7 +478,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
         if (p.loss_out && p.loss_terms) {
             __threadfence();
             unsigned t = 0;
-            if (lane == 0) t = atomicAdd(p.ticket, 1u);
+            if (lane == 0) t = atomicAdd(p.ticket, 1u) + (HIPE_RES_SELFVALID ? 1u : 0u);   // preset to ~0 / 0
             t = __shfl_sync(0xffffffffu, t, 0);
             if (t == gridDim.x - 1) {
                 __threadfence();
@@ -861,7 +932,11 @@ extern "C" int hipe_joint_loss_resident(const void* logits, int dtype, long long
     if (grid > p.n_items) grid = p.n_items;
 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+#if HIPE_RES_SELFVALID
+    e = cudaMemsetAsync(workspace, 0xFF, (size_t)need, st);   // every word "unset" (err, ticket: ~0)
+#else
     e = cudaMemsetAsync(workspace, 0, cb, st);
+#endif
     if (e != cudaSuccess) return (int)e;
     void* args[] = {(void*)&p};
     e = cudaLaunchCooperativeKernel(kern, dim3((unsigned)grid), dim3(res::kThreads), args, smem, st);

@@ -64,6 +64,7 @@ struct Params {
     int reverse;
     int st_hint;     // gradient stores carry an L2 evict_first hint
     int resident;    // fused launch: every CTA's share fits the ring, pass 2 re-reads shared memory not L2/HBM
+    int rev;         // fused launch: the second pass walks the CTA's share backwards (L2 recency)
     int pol1, pol2;  // L2 policy of the TMA loads of pass 1 / pass 2: 0 normal, 1 evict_first, 2 evict_last
     // reduce outputs
     float* coords;
@@ -333,6 +334,8 @@ static int dispatch(Params p, int cluster, int variant, cudaStream_t st) {
     // memory reads only: from global memory it would fetch every 32-byte sector twice)
     p.nv2 = (tma && p.G % 2 == 0) ? 1 : 0;
     if (const char* e = getenv("HIPE_NV2")) p.nv2 = (p.nv2 && e[0] != '0') ? 1 : 0;
+    p.rev = (kOp == OP_FUSED) ? 1 : 0;
+    if (const char* e = getenv("HIPE_FUSED_REV")) p.rev = (p.rev && e[0] != '0') ? 1 : 0;
     p.st_hint = 0;
     if (const char* e = getenv("HIPE_ST_HINT")) p.st_hint = (e[0] != '0') ? 1 : 0;
     return tma ? launch_stream<T, true, kOp>(p, S, st) : launch_stream<T, false, kOp>(p, S, st);

@@ -382,10 +382,31 @@ __device__ __forceinline__ void write_pass(const Params& p, const Tile& t, unsig
         for (int j = 0; j < VEC; ++j) ax[j] = kx * (float)((double)(x0i + j) - Ex);
     }
     const uint64_t st_pol = policy_evict_first();
-    float yf = (float)(row_first % p.H), zf = (float)(row_first / p.H);
     const float dyf = (float)(p.R % p.H), dzf = (float)(p.R / p.H), Hf = (float)p.H;
+    // Stage order.  The second pass of a fused launch walks the CTA's share BACKWARDS: the bytes
+    // read last are the ones most likely still in L2 (the re-read distance of stage i is
+    // ~2*(nst-i) stages x the resident CTAs instead of a constant 2*nst), measured on bf16 64^3 as
+    // the difference between re-reading everything from HBM and hitting L2 for the tail.
+    const bool rev = p.rev && !resident;
+    const int srows = kPasses * p.R;                       // rows a stage advances
+    const float sdy = (float)(srows % p.H), sdz = (float)(srows / p.H);
+    float ys, zs;                                          // first row of the current stage (this thread)
+    {
+        const int row_s = row_first + (rev ? (t.nst - 1) * srows : 0);
+        ys = (float)(row_s % p.H);
+        zs = (float)(row_s / p.H);
+    }
 
-    for (int i = 0; i < t.nst; ++i, ++it) {
+    for (int ii = 0; ii < t.nst; ++ii, ++it) {
+        const int i = rev ? t.nst - 1 - ii : ii;
+        float yf = ys, zf = zs;
+        if (rev) {
+            ys -= sdy; zs -= sdz;
+            if (ys < 0.f) { ys += Hf; zs -= 1.f; }
+        } else {
+            ys += sdy; zs += sdz;
+            if (ys >= Hf) { ys -= Hf; zs += 1.f; }
+        }
         float v[kPasses][VEC];
         uint32_t sbase = 0;
         if constexpr (kTma) {
@@ -496,7 +517,8 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers, !kTma ? 1
                 const int total = t.nst * (p.resident ? 1 : kNumPassesOverVolume);
                 for (int it = 0; it < total; ++it) {
                     const int slot = it % kStages;
-                    const int i = (it >= t.nst) ? it - t.nst : it;
+                    // second pass of a fused launch: LAST stage first (see write_pass)
+                    const int i = (it >= t.nst) ? (p.rev ? 2 * t.nst - 1 - it : it - t.nst) : it;
                     if (it >= kStages) mbar_wait(smem_u32(&sm.empty[slot]), ((it / kStages) - 1) & 1);
                     const long long off = (long long)i * t.stage_bytes;
                     const long long left = t.cta_bytes - off;

@@ -253,7 +253,7 @@ def resident_timed_out(device, n_vol):
     ws = _WORKSPACES.get((dev.index, torch.cuda.current_stream(dev).cuda_stream))
     if ws is None:
         return False
-    return bool(ws[4 * n_vol:4 * n_vol + 4].view(torch.int32).item() != 0)
+    return bool(ws[4 * n_vol:4 * n_vol + 4].view(torch.int32).item() == 1)
 
 
 def joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm, loss_out=None):

@@ -46,7 +46,8 @@ BF16_B = os.environ.get("HIPE_NCU_BF16_B", "64")     # batch the bf16 forward ca
 for name, key, cfgkey in [("%s_resident_f32" % tag, "resident", "f32_64_B64"),
                           ("%s_fwd_f32" % tag, "softargmax_fwd", "f32_64_B64"),
                           ("%s_fwd_bf16" % tag, "softargmax_fwd", "bf16_64_B%s" % BF16_B),
-                          ("%s_bwd_f32" % tag, "softargmax_bwd", "f32_64_B64"), ("%s_fused_f32" % tag, "fused", "f32_64_B64")]:
+                          ("%s_bwd_f32" % tag, "softargmax_bwd", "f32_64_B64"), ("%s_fused_f32" % tag, "fused", "f32_64_B64"),
+                          ("%s_fused_bf16" % tag, "fused", "bf16_64_B128")]:
     rep = os.path.join(ROOT, "gpurun_out", name + ".ncu-rep")
     if not os.path.exists(rep):
         continue
