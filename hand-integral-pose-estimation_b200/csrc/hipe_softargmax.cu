@@ -95,6 +95,7 @@ struct SmemLayout {
     float all_m[kMaxCluster];
     double finE[3];                // Ex, Ey, Ez (voxel units)
     float fin[5];                  // M, L, gx, gy, gz
+    double tgt[6];                 // fused: gt[0..2], vis[0..2] of the volume, fetched before the reduce pass
 };
 
 __device__ __forceinline__ void consumer_barrier() {

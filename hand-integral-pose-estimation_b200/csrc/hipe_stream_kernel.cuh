@@ -493,6 +493,15 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers, !kTma ? 1
     t.nst = (int)((t.cta_bytes + t.stage_bytes - 1) / t.stage_bytes);
     t.src = p.in + vol * p.vol_bytes + (long long)t.r0 * t.row_bytes;
 
+    if constexpr (kOp == OP_FUSED) {
+        // targets of this volume: their global-memory latency is paid under the reduce pass, not
+        // in the serial section between the passes (0.6-0.7 % on fp32 56^3 / 64^3, same-box A/B)
+        if (tid < 6) {
+            const void* base = tid < 3 ? p.gt : p.vis;
+            const long long j = vol * 3 + (tid < 3 ? tid : tid - 3);
+            sm.tgt[tid] = p.tgt_f64 ? reinterpret_cast<const double*>(base)[j] : (double)reinterpret_cast<const float*>(base)[j];
+        }
+    }
     if constexpr (kTma) {
         if (tid == 0) {
 #pragma unroll
@@ -569,10 +578,7 @@ __global__ void __launch_bounds__(kTma ? kConsumers + 32 : kConsumers, !kTma ? 1
                 const double c[3] = {(double)cxn, (double)cyn, (double)czn};
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
-                    const double tk = p.tgt_f64 ? reinterpret_cast<const double*>(p.gt)[vol * 3 + k]
-                                                : (double)reinterpret_cast<const float*>(p.gt)[vol * 3 + k];
-                    const double wk = p.tgt_f64 ? reinterpret_cast<const double*>(p.vis)[vol * 3 + k]
-                                                : (double)reinterpret_cast<const float*>(p.vis)[vol * 3 + k];
+                    const double tk = sm.tgt[k], wk = sm.tgt[3 + k];
                     const double dlt = c[k] - tk;
                     const double sg = (dlt > 0.0) ? 1.0 : ((dlt < 0.0) ? -1.0 : 0.0);
                     g[k] = (float)(sg * wk * p.norm);
