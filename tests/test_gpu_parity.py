@@ -183,6 +183,41 @@ def test_bf16_forward_backward():
         assert (np.abs(got - want) <= ulp + 1e-12).all()
 
 
+@pytest.mark.parametrize("geom", [(64, 64, 64), (56, 56, 56), (16, 16, 16)])
+def test_bf16_module_default_plan_vs_oracle(geom):
+    """bf16 heatmaps through the drop-in module with its own launch plan (the streaming single
+    launch for volumes >= 256 KB, forward + recompute backward below): loss to 1e-5, gradient
+    within 1 bf16 ulp of the rounded fp64 reference, on the rounded input."""
+    from hipe_b200 import ops
+    from nets import loss as L
+    D, H, W = geom
+    J, B = 21, 2
+    hm32 = synth.heatmaps(B, J, D, H, W, "peaked", seed=14)
+    gt, vis = synth.targets(B, J, seed=14, zero_vis_frac=0.1)
+    xb = _cuda(hm32).to(torch.bfloat16)
+    up = xb.float().cpu().numpy().astype(np.float64)
+    plan = ops.fused_plan(xb, B * J, D, H, W)
+    assert plan == ("stream" if D * H * W * 2 >= (1 << 18) else None)
+    x = xb.clone().requires_grad_(True)
+    ops.KERNEL_EVENTS = {}
+    try:
+        loss = L.JointLocationLoss()(x, _cuda(gt), _cuda(vis))
+        loss.backward()
+        assert ("joint_loss_fused" in ops.KERNEL_EVENTS) == (plan == "stream")
+    finally:
+        ops.KERNEL_EVENTS = None
+    ref_loss, ref_c = O.joint_location_loss(up, gt, vis, return_coords=True)
+    assert abs(loss.item() - ref_loss) <= 1e-5 * abs(ref_loss)
+    refg = O.joint_location_loss_grad(up, gt, vis)
+    want = torch.as_tensor(refg).to(torch.bfloat16).float().numpy().reshape(B * J, -1)
+    assert x.grad.dtype == torch.bfloat16
+    got = x.grad.float().cpu().numpy().reshape(B * J, -1)
+    ulp = np.maximum(np.abs(want), 1e-30) * 2.0 ** -7
+    c_close = (np.abs(ref_c - gt) < 1e-5).reshape(B * J, 3).any(axis=1)   # sign(c - gt) undecidable there
+    ok = (np.abs(got - want) <= ulp + 1e-12).all(axis=1) | c_close
+    assert ok.all()
+
+
 def test_plain_expectations_and_volume_softmax():
     from nets import loss as L
     D, H, W = 16, 12, 24
