@@ -67,3 +67,28 @@ def test_product_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+
+
+def test_launch_plan_host_logic():
+    """ops.fused_plan is pure host logic (dtype, geometry, the library's tiling query): the plan
+    table of DESIGN.md 3.2 without a GPU."""
+    import torch
+    from hipe_b200 import ops
+
+    def plan(dtype, n_vol, d):
+        x = torch.empty(0, dtype=dtype)
+        return ops._fused_plan(x, n_vol, d, d, d)
+
+    assert plan(torch.float32, 1344, 64) == "resident"
+    assert plan(torch.float32, 42, 64) == "stream"          # too few volumes for the persistent grid
+    assert plan(torch.float32, 2016, 56) == "stream"
+    assert plan(torch.float32, 672, 96) == "stream"
+    assert plan(torch.float32, 1344, 32) is None            # 128 KB volumes: forward + recompute backward
+    assert plan(torch.bfloat16, 2688, 64) == "stream"
+    assert plan(torch.bfloat16, 4032, 56) == "stream"
+    assert plan(torch.bfloat16, 2688, 32) is None
+    assert plan(torch.float64, 1344, 64) is None
+    # the tiling query behind "resident": supported geometries report a workspace size, others 0
+    lib = __import__("hipe_b200._lib", fromlist=["load"]).load()
+    assert lib.hipe_resident_workspace_bytes(0, 1344, 64, 64, 64) > 0
+    assert lib.hipe_resident_workspace_bytes(0, 1344, 5, 6, 7) == 0
