@@ -242,16 +242,28 @@ static int check_device() {
 }
 
 static int pick_cluster(int op, long long n_vol, long long vol_bytes, int NR, int esz) {
-    // Write-only and fused launches: aim for >= ~8 waves of 3 resident CTAs over 148 SMs while
+    // Write-only launches: aim for >= ~8 waves of 3 resident CTAs over 148 SMs while
     // keeping every CTA's share >= 64 KB (finer grain = shorter tail; no reduction to pay for).
     // Reduce-only launches pay a cluster barrier + DSMEM merge per CTA, so they split a volume
-    // only when there are too few volumes to fill the machine twice over (measured on B200:
-    // 1344 x 1 MiB volumes run 0.236 ms at S=1, 0.291 ms at S=4).
+    // only when there are fewer volumes than two per SM (measured on B200, fp32 64^3: 1344 volumes
+    // 0.236 ms at S=1, 0.291 at S=4; 672 volumes 0.119 at S=1, 0.123 at S=2; 336 volumes 0.062 at
+    // S=1, 0.070 at S=2, 0.072 at S=4; bf16 672 volumes 0.084 at S=1, 0.095 at S=2).
+    // Fused launches (reduce, meet, write) want a share of 256-450 KB per CTA for 4-byte logits and
+    // up to ~900 KB for 2-byte logits -- smaller shares pay the serial section between the passes
+    // too often, larger ones lose the L2 re-read -- and at least ~8 CTAs per SM in the grid.
+    // Measured (fused_ms at S = 1/2/4/8): fp32 64^3 x 1344: -/0.625/0.570/0.692, x 672:
+    // 0.340/0.308/0.291/0.359; 56^3 x 2016: 0.594/0.564/0.614/-, x 672: 0.232/0.205/0.216/0.291,
+    // x 336: 0.148/0.123/0.115/0.156; 96^3 x 672: -/-/1.035/0.999; bf16 64^3 x 2688:
+    // 0.613/0.660/-/-; bf16 96^3 x 672: 0.603/0.588/0.595/-.
+    if (op == OP_FUSED) {
+        const long long max_share = (esz == 2) ? (896ll << 10) : (448ll << 10);
+        int S = 1;
+        while (S < 8 && vol_bytes / S > max_share && NR / (2 * S) >= 1) S *= 2;
+        while (S < 8 && n_vol * S < 148ll * 8 && vol_bytes / (2 * S) >= (128ll << 10) && NR / (2 * S) >= 1) S *= 2;
+        return S;
+    }
     const bool reduce_only = (op == OP_REDUCE_SOFTMAX || op == OP_REDUCE_PLAIN);
-    // Fused launches on 2-byte logits want half the split (bf16 64^3 x 2688 volumes: 0.635 ms at
-    // S=1, 0.679 at S=2, 0.813 at S=4; x 1344: 0.336 / 0.355 / 0.414; 56^3 x 4032: 0.641 at S=1,
-    // 0.768 at S=2; 96^3 x 672: 0.615 / 0.592 / 0.600).
-    const long long want = reduce_only ? 148ll * 6 : (op == OP_FUSED && esz == 2) ? 148ll * 6 : 148ll * 24;
+    const long long want = reduce_only ? 148ll * 2 : 148ll * 24;
     const long long min_share = reduce_only ? 131072 : 65536;
     int S = 1;
     while (S < kMaxCluster && n_vol * S < want && vol_bytes / (2 * S) >= min_share && NR / (2 * S) >= 1) S *= 2;
