@@ -213,19 +213,21 @@ def _fused_plan(logits, n_vol, D, H, W):
     """Which launch computes loss + gradient fastest for this geometry, from B200 measurements
     (profiles/r1_configs.md): "resident" (persistent on-chip launch, one HBM read + one write)
     for the fp32 geometry it is tuned for -- 256-byte rows, volumes <= 1 MiB, i.e. 21x64^3;
-    "stream" (one launch, second read from L2) for other fp32 volumes >= 512 KiB and for bf16
-    volumes >= 256 KiB (bf16 64^3 x 2688: 0.635 ms vs 0.701 for the pair; 56^3 x 4032: 0.641 vs
-    0.715; 96^3 x 672: 0.592 vs 0.642; equal at 10752 volumes); None = the two-launch forward +
-    recompute backward."""
+    "stream" (one launch, second read through L2) for every other fp32 / bf16 volume >= 128 KiB:
+    with the backwards second pass and the share-sized clusters it beats the pair at every size
+    measured (fp32 32^3 x 5376: 0.275 ms vs 0.335, 40^3 x 672: 0.082 vs 0.103, 48^3 x 2016: 0.361
+    vs 0.419, 56^3 x 672: 0.203 vs 0.232, 96^3 x 672: 0.98 vs 1.08; bf16 48^3 x 5376: 0.564 vs
+    0.626, 64^3 x 2688: 0.61 vs 0.70, 96^3 x 672: 0.59 vs 0.64); None = the two-launch forward +
+    recompute backward, which still wins on tiny volumes (fp32 16^3: 0.366 ms vs 0.433 fused;
+    bf16 32^3 is a tie)."""
     esz = logits.element_size()
     vol_bytes = D * H * W * esz
-    if logits.dtype == torch.bfloat16:
-        return "stream" if (W * esz) % 16 == 0 and vol_bytes >= (1 << 18) else None
-    if logits.dtype != torch.float32:
+    if logits.dtype not in (torch.float32, torch.bfloat16):
         return None
-    if W * 4 == 256 and vol_bytes <= (1 << 20) and n_vol >= 296 and resident_supported(logits, n_vol, D, H, W):
+    if (logits.dtype == torch.float32 and W * 4 == 256 and vol_bytes <= (1 << 20) and n_vol >= 296
+            and resident_supported(logits, n_vol, D, H, W)):
         return "resident"
-    if (W * 4) % 16 == 0 and vol_bytes >= (1 << 19):
+    if (W * esz) % 16 == 0 and vol_bytes >= (1 << 17):
         return "stream"
     return None
 

@@ -83,7 +83,8 @@ def test_launch_plan_host_logic():
     assert plan(torch.float32, 42, 64) == "stream"          # too few volumes for the persistent grid
     assert plan(torch.float32, 2016, 56) == "stream"
     assert plan(torch.float32, 672, 96) == "stream"
-    assert plan(torch.float32, 1344, 32) is None            # 128 KB volumes: forward + recompute backward
+    assert plan(torch.float32, 1344, 32) == "stream"        # 128 KB volumes
+    assert plan(torch.float32, 1344, 16) is None            # 16 KB volumes: forward + recompute backward
     assert plan(torch.bfloat16, 2688, 64) == "stream"
     assert plan(torch.bfloat16, 4032, 56) == "stream"
     assert plan(torch.bfloat16, 2688, 32) is None

@@ -168,8 +168,8 @@ def test_module_uses_resident_launch_and_scales_upstream_gradient():
 
 
 def test_default_module_picks_the_measured_fastest_launch():
-    """fused=None: 21x64^3 fp32 batches go to the resident launch, other fp32 volumes >= 512 KB to
-    the streaming fused launch (bf16: >= 256 KB), small volumes to forward + recompute backward."""
+    """fused=None: 21x64^3 fp32 batches go to the resident launch, other volumes >= 128 KB to the
+    streaming fused launch, smaller volumes to forward + recompute backward."""
     from hipe_b200 import ops
     from nets import loss as L
     x64 = torch.empty((16, 21 * 64, 64, 64), device="cuda")
