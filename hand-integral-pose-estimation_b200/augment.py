@@ -1,12 +1,29 @@
-"""Drop-in for the hot-path functions of the reference's common/augment.py:
-`compute_similarity_transform` (:18-77), `get_joint_location_result` (:160-184) and the
-per-sample coordinate chain `trans_coords_from_patch_to_org_3d` (:196-217) / `pixel2cam`
-(:89-103), running on the sm_100a kernels.  The reference's image/patch augmentation code is out of scope."""
+"""Drop-in for the reference's common/augment.py.
+
+When the reference's own common/augment.py is further down sys.path (the INTEGRATION.md set-up),
+its source is executed in this module first, so every name the rest of the reference imports
+from `augment` (get_aug_config, generate_patch_image, trans_point2d, prepare_panet_input,
+test_get_joint_loc_res, projectPoints, gen_trans_from_patch_cv, ...: data/dataset.py:112-243,
+data/FreiHand/FreiHand.py:745,865,888, common/nets/loss.py:141,169,228-229) is the reference's
+own; then the hot-path functions below replace theirs with the sm_100a kernels:
+
+    compute_similarity_transform          augment.py:18-77    (+ a batched form)
+    get_joint_location_result             augment.py:160-184
+    trans_coords_from_patch_to_org_3d     augment.py:196-217  numpy callers; tensors go to the reference's
+    pixel2cam                             augment.py:89-103
+
+Without a reference tree on the path only these functions exist (`REFERENCE_AUGMENT` is None)."""
 import numpy as np
 import torch
 
-from hipe_b200 import evaluate as _ev
-from nets.loss import FreiHandConfig, softmax_integral_tensor
+from hipe_b200 import _overlay
+
+REFERENCE_AUGMENT, REFERENCE_AUGMENT_ERROR = _overlay.exec_shadowed(globals(), __file__, "augment.py")
+_ref_trans3d = globals().get("trans_coords_from_patch_to_org_3d") if REFERENCE_AUGMENT_ERROR is None else None
+_ref_pixel2cam = globals().get("pixel2cam") if REFERENCE_AUGMENT_ERROR is None else None
+
+from hipe_b200 import evaluate as _ev                                   # noqa: E402
+from nets.loss import FreiHandConfig, softmax_integral_tensor           # noqa: E402
 
 
 def compute_similarity_transform(X, Y, compute_optimal_scale=False):
@@ -47,7 +64,13 @@ def _one(a, shape):
 def trans_coords_from_patch_to_org_3d(coords_in_patch, c_x, c_y, bb_width, bb_height, patch_width, patch_height,
                                       scale, trans, tprime, p=False):
     """augment.py:196-217 for one (J, C>=3) sample, numpy in / numpy out (same positional
-    signature; like the reference only `trans` and `tprime` enter the arithmetic)."""
+    signature; like the reference only `trans` and `tprime` enter the arithmetic).  Tensor inputs
+    (prepare_panet_input's differentiable use, augment.py:556-574) take the reference's own code."""
+    if isinstance(coords_in_patch, torch.Tensor):
+        if _ref_trans3d is None:
+            raise TypeError("tensor inputs need the reference's common/augment.py on sys.path")
+        return _ref_trans3d(coords_in_patch, c_x, c_y, bb_width, bb_height, patch_width, patch_height, scale,
+                            trans, tprime, p)
     c = np.asarray(coords_in_patch, dtype=np.float64)
     J = c.shape[0]
     K = np.eye(3)[None]
@@ -61,6 +84,8 @@ def trans_coords_from_patch_to_org_3d(coords_in_patch, c_x, c_y, bb_width, bb_he
 def pixel2cam(pixel_coord, K, pp=False):
     """augment.py:89-103 for one (J, 3) sample: K^-1 (u, v, 1) z / 1000.  (The reference also
     divides the caller's z column by 1000 in place; so does this.)"""
+    if isinstance(pixel_coord, torch.Tensor) and _ref_pixel2cam is not None:
+        return _ref_pixel2cam(pixel_coord, K, pp)
     pc = np.asarray(pixel_coord, dtype=np.float64)
     J = pc.shape[0]
     ident = np.array([[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.0, 0.0, 1.0]])

@@ -7,7 +7,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(os.path.dirname(HERE), "csrc")
 LIB_PATH = os.path.join(HERE, "libhipe_b200.so")
-SOURCES = ["hipe_softargmax.cu", "hipe_resident.cu", "hipe_eval.cu", "hipe_metrics.cu", "hipe_exchange.cu", "hipe_host.cu"]
+SOURCES = ["hipe_softargmax.cu", "hipe_resident.cu", "hipe_cluster.cu", "hipe_eval.cu", "hipe_metrics.cu", "hipe_exchange.cu", "hipe_host.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--use_fast_math=false",

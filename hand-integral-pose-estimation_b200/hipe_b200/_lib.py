@@ -29,6 +29,10 @@ SIGNATURES = {
     "hipe_resident_workspace_bytes": (_ll, [_i, _ll, _i, _i, _i]),
     "hipe_joint_loss_resident": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp, _vp,
                                       _vp, _ll, _vp]),
+    "hipe_cluster_workspace_bytes": (_ll, [_i, _ll, _i, _i, _i]),
+    "hipe_cluster_plan": (_i, [_i, _ll, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "hipe_joint_loss_cluster": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp, _vp,
+                                     _vp, _ll, _vp]),
     "hipe_scale_inplace": (_i, [_vp, _i, _ll, _vp, _vp]),
     "hipe_scale_inplace_s": (_i, [_vp, _i, _ll, _vp, _i, _vp]),
     "hipe_sum_f64": (_i, [_vp, _ll, _d, _vp, _vp]),

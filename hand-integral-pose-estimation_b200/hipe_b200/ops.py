@@ -196,7 +196,7 @@ def sum_f64(x, scale=1.0):
 
 
 # "auto": the launch measured fastest for the geometry (fused_plan); "resident" / "stream" force one
-FUSED_MODE = "auto"          # "auto" | "resident" | "stream"
+FUSED_MODE = "auto"          # "auto" | "cluster" | "resident" | "stream"
 
 
 _PLAN_CACHE = {}
@@ -290,12 +290,60 @@ def joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm, loss_out=None):
     return coords, expect, stats, terms, dlogits
 
 
+def cluster_plan(logits, n_vol, D, H, W):
+    """(cluster size, ring slots per CTA, stages per CTA share, bytes per stage) of the
+    cluster-resident launch for this geometry, or None when it cannot take it."""
+    import ctypes
+    c, ns, sh, sb = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    rc = _lib.load().hipe_cluster_plan(_logits_code(logits), n_vol, D, H, W, ctypes.byref(c), ctypes.byref(ns),
+                                       ctypes.byref(sh), ctypes.byref(sb))
+    return None if rc != 0 else (c.value, ns.value, sh.value, sb.value)
+
+
+def cluster_supported(logits, n_vol, D, H, W):
+    return _lib.load().hipe_cluster_workspace_bytes(_logits_code(logits), n_vol, D, H, W) > 0
+
+
+def joint_loss_cluster(logits, n_vol, D, H, W, gt, vis, norm, loss_out=None):
+    """hipe_joint_loss_cluster: same outputs as joint_loss_fused; each volume lives in the shared
+    memory of one thread-block cluster between the reduction and the gradient write."""
+    _need_cuda(logits, "heatmaps")
+    code = _logits_code(logits)
+    if not logits.is_contiguous():
+        logits = logits.contiguous()
+    dev = logits.device
+    lib = _lib.load()
+    need = lib.hipe_cluster_workspace_bytes(code, n_vol, D, H, W)
+    if need <= 0:
+        raise _lib.HipeError("libhipe_b200: error %d: geometry not supported by the cluster launch"
+                             % _lib.E_UNSUPPORTED)
+    coords = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
+    gt, vis, tcode, _ = _targets(coords, gt, vis)
+    if gt.numel() != n_vol * 3 or vis.numel() != n_vol * 3:
+        raise ValueError("targets must hold 3 values per volume")
+    expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev)
+    stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
+    terms = torch.empty((n_vol * 3,), dtype=torch.float64, device=dev)
+    dlogits = torch.empty_like(logits)
+    with _on(dev):
+        ws = _workspace(dev, need)
+        with _launch("joint_loss_cluster", logits):
+            check(lib.hipe_joint_loss_cluster(
+                logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
+                coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), _ptr(loss_out),
+                dlogits.data_ptr(), ws.data_ptr(), ws.numel(), _stream(logits)))
+    return coords, expect, stats, terms, dlogits
+
+
 def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, variant=None, mode=None, loss_out=None):
     """One launch: coords, expect, stats, per-coordinate loss terms (n_vol*3 fp64), dlogits.
     `loss_out` (0-dim fp64 CUDA tensor, optional) is filled with the loss scalar: by the resident
     launch itself, else by hipe_sum_f64."""
     _need_cuda(logits, "heatmaps")
     mode = FUSED_MODE if mode is None else mode
+    if mode == "cluster" or (mode == "auto" and cluster is None and variant is None
+                             and fused_plan(logits, n_vol, D, H, W) == "cluster"):
+        return joint_loss_cluster(logits, n_vol, D, H, W, gt, vis, norm, loss_out)
     if mode == "resident" or (mode == "auto" and cluster is None and variant is None
                               and fused_plan(logits, n_vol, D, H, W) == "resident"):
         try:
@@ -487,8 +535,11 @@ class IntegralL1Function(torch.autograd.Function):
 
 class FusedJointLossFunction(torch.autograd.Function):
     """JointLocationLoss forward with the gradient produced in the same launch
-    (hipe_joint_loss_fused): backward only scales the stored dlogits when the upstream
-    gradient is not 1."""
+    (hipe_joint_loss_cluster / _resident / _fused): backward only scales the stored dlogits when the
+    upstream gradient is not 1, and hands the buffer over.  The stored gradient is CONSUMED by that
+    hand-over (scaled in place, possibly adopted by autograd as `.grad`): a second backward through
+    the same forward (retain_graph=True) raises instead of silently compounding the scale -- use
+    JointLocationLoss(fused=False) for graphs that are back-propagated more than once."""
 
     @staticmethod
     def forward(ctx, heatmap_out, gt, vis, num_joints, D, H, W, norm, reduce_loss=True):
@@ -501,15 +552,22 @@ class FusedJointLossFunction(torch.autograd.Function):
         loss64 = torch.empty((), dtype=torch.float64, device=heatmap_out.device)
         coords, _, _, terms, dlogits = joint_loss_fused(heatmap_out, n_vol, D, H, W, gt, vis, norm,
                                                         loss_out=loss64 if reduce_loss else None)
-        loss = loss64.to(out_dtype)
-        ctx.save_for_backward(dlogits)
+        loss = loss64 if out_dtype == torch.float64 else loss64.to(out_dtype)
+        ctx.dlogits = dlogits                    # not save_for_backward: it is mutated, once, by backward
         ctx.in_shape = heatmap_out.shape
+        coords = coords.view(B, num_joints * 3)
         ctx.mark_non_differentiable(coords, terms)
-        return loss, coords.view(B, num_joints * 3), terms
+        return loss, coords, terms
 
     @staticmethod
     def backward(ctx, grad_loss, _grad_coords, _grad_terms):
-        (dlogits,) = ctx.saved_tensors
+        dlogits = ctx.dlogits
+        if dlogits is None:
+            raise RuntimeError(
+                "hipe_b200: second backward through the single-launch JointLocationLoss: its heatmap "
+                "gradient was stored by the forward launch and handed over (scaled in place) by the first "
+                "backward.  Build the criterion with fused=False for retain_graph / repeated backward.")
+        ctx.dlogits = None
         # in place, on device, no host sync; the kernel returns at once when the scalar is 1
         gs = grad_loss
         if gs.device != dlogits.device or gs.dtype not in (torch.float32, torch.float64) or not gs.is_contiguous():

@@ -1,12 +1,46 @@
-"""Drop-in for the SVD-backed functions of procrustes_encoding/nrsfm/nrsfm_modules.py:
-`batch_det_3x3` (:24-43) and `make_orthonormal` (:46-67).  The reference takes its batched SVD
-from the external, un-vendored torch_batch_svd extension (nrsfm/batch_svd.py:5-35); here both
-directions are one hand-written sm_100a kernel each (one thread per 3x3 matrix, Jacobi SVD in
-fp64 registers).  The sparse-coding layers of that file are dense linear algebra outside the
-hot path and are not rebuilt.  CUDA tensors only."""
+"""Drop-in for procrustes_encoding/nrsfm/nrsfm_modules.py: `batch_det_3x3` (:24-43) and
+`make_orthonormal` (:46-67) on the sm_100a kernels.  The reference takes its batched SVD from the
+external, un-vendored torch_batch_svd extension (nrsfm/batch_svd.py:5-35); here both directions are
+one hand-written kernel each (one thread per 3x3 matrix, Jacobi SVD in fp64 registers).
+
+`nrsfm` is a namespace package in the reference (no __init__.py) and here, so with this package's
+directory in front of procrustes_encoding/ on sys.path the two directories merge and only this
+module shadows its namesake.  Its sparse-coding layers (SfMSparseCodingLayer, ...: :70-230, dense
+linear algebra outside the hot path) are needed by nrsfm/nrsfmnet.py:5, so the reference's own
+source of this module is executed here first (hipe_b200._overlay) and the two functions below
+replace theirs.  If torch_batch_svd is not installed the reference's `.batch_svd` import is
+satisfied by a stub that raises when called (make_orthonormal no longer calls it).  CUDA tensors only."""
+import sys
+import types
+
 import torch
 
-from hipe_b200 import ops
+from hipe_b200 import _overlay, ops
+
+
+def _stub_batch_svd():
+    name = (__package__ + "." if __package__ else "") + "batch_svd"
+    if name in sys.modules:
+        return
+    try:
+        import torch_batch_svd  # noqa: F401
+        return
+    except Exception:
+        pass
+    m = types.ModuleType(name)
+
+    def batch_svd(x):
+        raise RuntimeError("torch_batch_svd is not installed; hipe_b200 replaces its only use "
+                           "(make_orthonormal) with hipe_orthonormalize3_fwd/_bwd")
+
+    m.batch_svd = batch_svd
+    m.__hipe_stub__ = True
+    sys.modules[name] = m
+
+
+if _overlay.find_shadowed(__file__, "nrsfm/nrsfm_modules.py") is not None:
+    _stub_batch_svd()
+REFERENCE_MODULE, REFERENCE_MODULE_ERROR = _overlay.exec_shadowed(globals(), __file__, "nrsfm/nrsfm_modules.py")
 
 
 def batch_det_3x3(x):

@@ -152,6 +152,29 @@ HIPE_API int hipe_joint_loss_resident(const void* logits_dev, int dtype, long lo
                              void* stream);
 
 /*
+ * The same contract again, as ONE persistent launch of thread-block CLUSTERS that hold each volume
+ * in distributed shared memory between the reduction and the gradient write (C CTAs x up to 14
+ * 16 KB TMA slots; the C partial sums travel CTA to CTA through st.shared::cluster + remote
+ * mbarrier arrives): HBM sees each volume once in and its gradient once out, the L2 holds nothing,
+ * and no role waits on global memory.  Takes every geometry whose volume fits one cluster's
+ * shared memory with look-ahead to spare (fp32 64^3 on 8 CTAs, bf16 64^3 and fp32 56^3 on 4).
+ *   workspace_dev : >= hipe_cluster_workspace_bytes(...) (256) bytes, 256-byte aligned
+ * Returns HIPE_E_UNSUPPORTED otherwise (hipe_cluster_workspace_bytes returns 0 in exactly those
+ * cases); hipe_cluster_plan reports the cluster size, ring slots per CTA, stages per CTA share and
+ * bytes per stage the launch would use.
+ */
+HIPE_API long long hipe_cluster_workspace_bytes(int dtype, long long n_vol, int D, int H, int W);
+HIPE_API int hipe_cluster_plan(int dtype, long long n_vol, int D, int H, int W, int* cluster, int* nslots,
+                      int* share_stages, int* stage_bytes);
+HIPE_API int hipe_joint_loss_cluster(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
+                            const void* gt_dev, const void* vis_dev, int tgt_dtype, double norm,
+                            float* coords_dev, double* expect_dev, float* stats_dev,
+                            double* loss_terms_dev /* n_vol*3 */,
+                            double* loss_dev /* nullable: norm * sum(loss_terms), by the last cluster */,
+                            void* dlogits_dev, void* workspace_dev, long long workspace_bytes,
+                            void* stream);
+
+/*
  * x[i] *= *gscale_dev for n elements of `dtype`, in place; returns without touching memory when
  * the scalar is exactly 1.  Used to apply an upstream loss gradient to the dlogits the fused
  * launch already produced, without a host synchronisation.

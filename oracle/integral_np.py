@@ -144,6 +144,23 @@ def combined_loss(heatmap_out, coord_teacher, gt_coord, gt_vis, labelled):
     return (sup + uns) / len(c), compute_mpjpe(c, gt_coord), compute_mpjpe(teacher, gt_coord), sup, uns
 
 
+def joint_location_loss2(heatmap_out, gt_label, joint_cam_normalized, R, trans, K, tprime, patch_width=224.0,
+                         patch_height=224.0):
+    """common/nets/loss.py:207-277: soft-argmax (:219), rescale to patch pixels (:229 =
+    common/augment.py:186-194), trans inverted (:232), per sample patch -> image with z + tprime
+    (:236-239), pixel2cam (:245), R^T (:249); the loss is the SUM over samples and joints of the
+    squared distance to joint_cam_normalized (:262-276; size_average is forced off at :270)."""
+    from oracle import chain_np
+    joint_num = int(np.asarray(gt_label).shape[1] / 3)
+    w, h, d = _dims_of(heatmap_out)
+    c = integral_coords(heatmap_out, joint_num, w, h, d)
+    patch = chain_np.joint_location_result(c, patch_width, patch_height)[..., 0:3]
+    tinv = np.linalg.inv(np.asarray(trans, dtype=np.float64))
+    _, cam = chain_np.camera_chain(patch, tinv, tprime, K, R=R)
+    diff = np.asarray(joint_cam_normalized, dtype=np.float64) - cam
+    return (diff ** 2).sum()
+
+
 def softmax_entropy(logits, J, D, H, W):
     """scipy.stats.entropy of each row of softmax_integral_tensor2's output
     (main/generate_correlation_graph.py:116-141 on common/nets/loss.py:61-67): -sum p ln p per

@@ -1,0 +1,101 @@
+"""Same-box A/B of the single-launch loss+gradient kernels (CUDA events, rotating inputs larger
+than L2): cluster-resident vs persistent L2-window (resident) vs streaming fused vs the pair.
+    python scripts/ab_cluster.py [quick]"""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (os.path.join(ROOT, "hand-integral-pose-estimation_b200"), ROOT):
+    sys.path.insert(0, p)
+import torch
+from hipe_b200 import ops
+
+J = 21
+PEAK = 6535.7
+try:
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    pass
+
+
+def timeit(fn, bufs, reps=30, warm=5):
+    for i in range(warm):
+        fn(bufs[i % len(bufs)])
+    torch.cuda.synchronize()
+    ts = []
+    for blk in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(reps):
+            fn(bufs[i % len(bufs)])
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1) / reps)
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def case(dt, D, B, envs):
+    n_vol = B * J
+    esz = 4 if dt == torch.float32 else 2
+    nbuf = max(3, int(400e6 // (n_vol * D ** 3 * esz)) + 1)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    bufs = []
+    for i in range(nbuf):
+        x = torch.randn(B, J * D, D, D, generator=g, device="cuda")
+        x.view(n_vol, -1)[:, 12345 % D ** 3] += 12.0
+        bufs.append(x.to(dt))
+    gt = torch.rand(B, 3 * J, generator=g, device="cuda", dtype=torch.float64) - 0.5
+    vis = torch.ones_like(gt)
+    byt = n_vol * 2 * D ** 3 * esz
+    out = {}
+
+    def rec(name, fn):
+        try:
+            med, mn = timeit(fn, bufs)
+            out[name] = med
+            print("  %-34s %.4f ms (min %.4f)  %6.0f GB/s  frac %.3f" % (name, med, mn, byt / med / 1e6, byt / med / 1e6 / PEAK), flush=True)
+        except Exception as e:
+            print("  %-34s FAILED %r" % (name, e), flush=True)
+
+    print("%s %d^3 x %d volumes (B=%d)" % ("fp32" if esz == 4 else "bf16", D, n_vol, B), flush=True)
+    loss = torch.empty((), dtype=torch.float64, device="cuda")
+    if ops.resident_supported(bufs[0], n_vol, D, D, D) and n_vol >= 296:
+        rec("resident", lambda x: ops.joint_loss_resident(x, n_vol, D, D, D, gt, vis, 1.0 / B, loss_out=loss))
+    rec("stream fused", lambda x: ops.joint_loss_fused(x, n_vol, D, D, D, gt, vis, 1.0 / B, mode="stream"))
+    for env in envs:
+        os.environ.update(env)
+        try:
+            plan = ops.cluster_plan(bufs[0], n_vol, D, D, D)
+            if plan is None:
+                print("  cluster %s: unsupported" % env)
+                continue
+            rec("cluster %s C=%d slots=%d share=%d" % (",".join("%s=%s" % (k[13:], v) for k, v in env.items()), plan[0], plan[1], plan[2]),
+                lambda x: ops.joint_loss_cluster(x, n_vol, D, D, D, gt, vis, 1.0 / B, loss_out=loss))
+        finally:
+            for k in env:
+                del os.environ[k]
+
+    def pair(x):
+        c, e, s = ops.softargmax_forward(x, n_vol, D, D, D)
+        _, gg = ops.l1_loss(c.view(B, 3 * J), gt, vis, 1.0 / B)
+        ops.softargmax_backward(x, n_vol, D, D, D, s, e, gg.view(-1, 3))
+    rec("pair fwd+l1+bwd (3V bytes: x1.5)", pair)
+    return out
+
+
+if __name__ == "__main__":
+    quick = "quick" in sys.argv
+    f32, bf = torch.float32, torch.bfloat16
+    case(f32, 64, 64, [{}, {"HIPE_CLUSTER_SLOTS": "13"}, {"HIPE_CLUSTER_SLOTS": "11"}, {"HIPE_CLUSTER_C": "6"}, {"HIPE_CLUSTER_C": "7"},
+                       {"HIPE_ST_HINT": "1"}])
+    case(bf, 64, 128, [{}, {"HIPE_CLUSTER_C": "8"}, {"HIPE_CLUSTER_C": "3"}, {"HIPE_CLUSTER_C": "5"}])
+    if not quick:
+        case(bf, 64, 512, [{}, {"HIPE_CLUSTER_C": "8"}])
+        case(bf, 64, 64, [{}, {"HIPE_CLUSTER_C": "8"}])
+        case(f32, 56, 32, [{}, {"HIPE_CLUSTER_C": "8"}, {"HIPE_CLUSTER_C": "7"}])
+        case(f32, 56, 96, [{}, {"HIPE_CLUSTER_C": "8"}, {"HIPE_CLUSTER_C": "7"}])
+        case(f32, 64, 32, [{}])
+        case(f32, 48, 96, [{}, {"HIPE_CLUSTER_C": "3"}])
+        case(f32, 32, 256, [{}, {"HIPE_CLUSTER_C": "2"}])

@@ -43,7 +43,7 @@ def load_loss_module():
     import torch.cuda.comm  # noqa: F401
 
     cfg_mod = types.ModuleType("config")
-    cfg_mod.cfg = types.SimpleNamespace(_lambda=0)
+    cfg_mod.cfg = types.SimpleNamespace(_lambda=0, patch_width=224, patch_height=224)
     saved = {k: sys.modules.get(k) for k in ("config", "augment", "config_panet", "FreiHand_config")}
     sys.modules["config"] = cfg_mod
     sys.modules["augment"] = types.ModuleType("augment")
@@ -143,6 +143,36 @@ def load_nrsfm_modules():
         spec.loader.exec_module(mod)
         _cache["nrsfm"] = mod
     return _cache["nrsfm"]
+
+
+def load_loss2_class():
+    """JointLocationLoss2 of the unmodified common/nets/loss.py (:207-277), runnable on CPU: its
+    module-level `augment` (a stub here) gets the reference's own test_get_joint_loc_res
+    (common/augment.py:186-194, source slice, with the same cfg), trans_coords_from_patch_to_org_3d
+    and pixel2cam (source slices, see load_chain_functions), and the one `.cuda()` of its result
+    (:268) is made an identity for the duration of a call."""
+    if "loss2" in _cache:
+        return _cache["loss2"]
+    import numpy as np
+    import torch
+    L = load_loss_module()
+    ch = load_chain_functions()
+    ns = {"np": np, "cfg": types.SimpleNamespace(patch_width=224, patch_height=224)}
+    exec(_slice("common/augment.py", 186, 194), ns)
+    L.augment.test_get_joint_loc_res = ns["test_get_joint_loc_res"]
+    L.augment.trans_coords_from_patch_to_org_3d = ch.trans_coords_from_patch_to_org_3d
+    L.augment.pixel2cam = ch.pixel2cam
+
+    def run(*args):
+        orig = torch.Tensor.cuda
+        torch.Tensor.cuda = lambda self, *a, **k: self
+        try:
+            return L.JointLocationLoss2()(*args)
+        finally:
+            torch.Tensor.cuda = orig
+
+    _cache["loss2"] = run
+    return run
 
 
 def fixture_arrays():

@@ -1,0 +1,146 @@
+"""GPU parity of the cluster-resident single launch (hipe_joint_loss_cluster: every volume held in
+the distributed shared memory of one thread-block cluster between the reduction and the gradient
+write) against the fp64 oracle.  Same gates as tests/test_gpu_parity.py."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import integral_np as O
+from tests import synth
+from tests.test_gpu_resident import _check, _cuda
+
+pytestmark = pytest.mark.gpu
+
+# geometry -> cluster size the launch picks (None: the volume does not fit one cluster)
+CLU_GEOMS = {
+    (16, 16, 16): 1,
+    (32, 32, 32): 1,
+    (64, 64, 64): 8,     # headline: 1 MiB on 8 CTAs x 8 stages
+    (56, 56, 56): 4,     # reference default (main/config.py:23-25): 14 stages of 12.25 KB per CTA
+    (48, 48, 48): 4,
+    (16, 128, 64): 4,    # stage = half a z-slice (SR | H, non-zero y base)
+    (12, 20, 24): 1,     # 30 rows per visit, 180 of 256 team threads active
+}
+UNSUPPORTED = [(96, 96, 96), (8, 8, 8), (5, 6, 7), (3, 9, 100)]
+
+
+@pytest.mark.parametrize("regime", ["noise", "peaked", "sharp"])
+@pytest.mark.parametrize("geom", list(CLU_GEOMS))
+def test_cluster_vs_oracle(geom, regime):
+    from hipe_b200 import ops
+    D, H, W = geom
+    J, B = 21, 2
+    hm = synth.heatmaps(B, J, D, H, W, regime, seed=11)
+    gt, vis = synth.targets(B, J, seed=11, zero_vis_frac=0.1)
+    x = _cuda(hm)
+    plan = ops.cluster_plan(x, B * J, D, H, W)
+    assert plan is not None and plan[0] == CLU_GEOMS[geom], plan
+    out = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    torch.cuda.synchronize()
+    worst = _check(hm, gt, vis, D, H, W, B, J, out)
+    print("cluster %s %s: worst gradient error / volume max = %.2e (gate 1e-5)" % (geom, regime, worst))
+
+
+@pytest.mark.parametrize("geom", UNSUPPORTED)
+def test_cluster_unsupported_geometries(geom):
+    from hipe_b200 import _lib, ops
+    D, H, W = geom
+    x = _cuda(synth.heatmaps(1, 21, D, H, W, "peaked", seed=3))
+    gt, vis = synth.targets(1, 21, seed=3)
+    assert not ops.cluster_supported(x, 21, D, H, W)
+    assert ops.cluster_plan(x, 21, D, H, W) is None
+    with pytest.raises(_lib.HipeError):
+        ops.joint_loss_cluster(x, 21, D, H, W, _cuda(gt), _cuda(vis), 1.0)
+
+
+@pytest.mark.parametrize("csize", [1, 2, 3, 4, 5, 6, 7, 8])
+def test_every_cluster_size(csize):
+    """Forced cluster sizes, powers of two or not (uneven shares): 32^3 fp32 has 8 stages."""
+    from hipe_b200 import ops
+    D = H = W = 32
+    J, B = 21, 3
+    hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=17)
+    gt, vis = synth.targets(B, J, seed=17)
+    x = _cuda(hm)
+    os.environ["HIPE_CLUSTER_C"] = str(csize)
+    try:
+        assert ops.cluster_plan(x, B * J, D, H, W)[0] == csize
+        out = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+        torch.cuda.synchronize()
+    finally:
+        del os.environ["HIPE_CLUSTER_C"]
+    _check(hm, gt, vis, D, H, W, B, J, out)
+
+
+def test_many_volumes_per_cluster_and_reproducible():
+    """More volumes than clusters (every role loops, ring laps and both exchange buffers are
+    reused many times), a count that is not a multiple of the cluster count, bit-reproducible."""
+    from hipe_b200 import ops
+    D = H = W = 64
+    J, B = 21, 9             # 189 volumes over <= 18 clusters of 8
+    hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=21)
+    gt, vis = synth.targets(B, J, seed=21, zero_vis_frac=0.1)
+    x = _cuda(hm)
+    loss = torch.full((), float("nan"), dtype=torch.float64, device="cuda")
+    out = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B, loss_out=loss)
+    torch.cuda.synchronize()
+    _check(hm, gt, vis, D, H, W, B, J, out)
+    ref = ops.sum_f64(out[3], 1.0 / B)
+    assert abs(loss.item() - ref.item()) <= 1e-14 * abs(ref.item())
+    out2 = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    assert torch.equal(out[4], out2[4]) and torch.equal(out[0], out2[0]) and torch.equal(out[3], out2[3])
+    # a small ring (2 slots of look-ahead only) and a tiny grid (one cluster walks everything)
+    for env in ({"HIPE_CLUSTER_SLOTS": "10"}, {"HIPE_CLUSTER_GRID": "1"}, {"HIPE_CLUSTER_GRID": "3"}):
+        os.environ.update(env)
+        try:
+            out3 = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+            torch.cuda.synchronize()
+        finally:
+            for k_ in env:
+                del os.environ[k_]
+        assert torch.equal(out[4], out3[4]) and torch.equal(out[0], out3[0])
+
+
+def test_cluster_agrees_with_two_launch_path():
+    from hipe_b200 import ops
+    D = H = W = 64
+    J, B = 21, 3
+    hm = synth.heatmaps(B, J, D, H, W, "sharp", seed=5)
+    gt, vis = synth.targets(B, J, seed=5)
+    x = _cuda(hm)
+    c1, e1, s1, t1, d1 = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    c0, e0, s0 = ops.softargmax_forward(x, B * J, D, H, W)
+    _, g = ops.l1_loss(c0.view(B, 3 * J), _cuda(gt), _cuda(vis), 1.0 / B)
+    d0 = ops.softargmax_backward(x, B * J, D, H, W, s0, e0, g.view(-1, 3))
+    assert (c1 - c0).abs().max().item() <= 2e-7
+    assert (e1 - e0).abs().max().item() <= 1e-5          # voxel units
+    same_sign = ((c1 - _cuda(gt).view(-1, 3)).sign() == (c0 - _cuda(gt).view(-1, 3)).sign()).all(dim=1)
+    scale = d0.view(B * J, -1).abs().amax(dim=1, keepdim=True)
+    rel = ((d1 - d0).view(B * J, -1).abs() / scale)[same_sign]
+    assert rel.max().item() <= 2e-5
+
+
+@pytest.mark.parametrize("D", [64, 48, 32])
+def test_cluster_bf16(D):
+    from hipe_b200 import ops
+    H = W = D
+    J, B = 21, 3
+    hm32 = synth.heatmaps(B, J, D, H, W, "peaked", seed=4)
+    gt, vis = synth.targets(B, J, seed=4)
+    xb = _cuda(hm32).to(torch.bfloat16)
+    up = xb.float().cpu().numpy().astype(np.float64)       # the rounded tensor is the oracle's input
+    assert ops.cluster_supported(xb, B * J, D, H, W)
+    coords, expect, stats, terms, d = ops.joint_loss_cluster(xb, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    ref_loss, ref_c = O.joint_location_loss(up, gt, vis, return_coords=True)
+    c = coords.view(B, 3 * J).cpu().numpy().astype(np.float64)
+    assert (np.abs(c - ref_c) <= 1e-5 * np.maximum(np.abs(ref_c), 0.5)).all()
+    assert abs(terms.sum().item() / B - ref_loss) <= 1e-5 * abs(ref_loss)
+    refg = O.joint_location_loss_grad(up, gt, vis)
+    want = torch.as_tensor(refg).to(torch.bfloat16).float().numpy().reshape(B * J, -1)
+    got = d.float().cpu().numpy().reshape(B * J, -1)
+    ulp = np.maximum(np.abs(want), 1e-30) * 2.0 ** -7
+    c_close = (np.abs(ref_c - gt) < 1e-5).reshape(B * J, 3).any(axis=1)
+    ok = (np.abs(got - want) <= ulp + 1e-12).all(axis=1) | c_close
+    assert ok.all()

@@ -103,6 +103,33 @@ def test_combined_loss_oracle():
     assert abs(sup - g["sup"]) < 1e-12 and abs(uns - g["unsup"]) < 1e-12
 
 
+@pytest.mark.parametrize("name", ["combined_cube16", "combined_cube64"])
+def test_combined_loss_oracle_larger_volumes(name):
+    """16^3 and 64^3 (the production volume): input regenerated from the seed, hash-checked."""
+    import hashlib
+    g = gold(name)
+    B, D, H, W = (int(v) for v in g["shape"])
+    hm = synth.heatmaps(B, 21, D, H, W, "peaked", seed=int(g["seed"]))
+    assert hashlib.sha256(np.ascontiguousarray(hm).tobytes()).hexdigest() == str(g["input_sha256"])
+    h64 = hm.astype(np.float64)
+    loss, smp, tmp, sup, uns = O.combined_loss(h64, g["teacher"], g["gt"], g["vis"], g["labelled"])
+    assert abs(loss - g["loss64"]) < 1e-12
+    assert abs(smp - g["student_mpjpe"]) < 1e-13 and abs(tmp - g["teacher_mpjpe"]) < 1e-14
+    assert abs(sup - g["sup"]) < 1e-11 and abs(uns - g["unsup"]) < 1e-11
+    # the gradient of the lambda = 0 total = JointLocationLoss against where(labelled, gt, teacher)
+    tgt = np.where(g["labelled"][:, None], g["gt"], g["teacher"][0])
+    grad = O.joint_location_loss_grad(h64, tgt, g["vis"]).reshape(B * 21, -1)
+    np.testing.assert_allclose(grad[:, g["grad_idx"]], g["grad64_sampled"], rtol=0, atol=1e-15)
+    np.testing.assert_allclose(np.abs(grad).max(axis=1), g["grad64_abs_max"], rtol=1e-10)
+
+
+def test_joint_location_loss2_oracle():
+    g = gold("loss2")
+    v = O.joint_location_loss2(g["logits"].astype(np.float64), g["gt_label"], g["joint_cam_normalized"], g["R"],
+                               g["trans"], g["K"], g["tprime"])
+    assert abs(v - g["loss64"]) <= 1e-12 * g["loss64"]
+
+
 @pytest.mark.parametrize("tag", ["freihand", "panet"])
 def test_procrustes_oracle_golden(tag):
     g = gold("procrustes")
