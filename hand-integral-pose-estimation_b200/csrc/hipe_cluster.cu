@@ -42,6 +42,7 @@
 // ratio of fp64 sums built from the same rounded fp32 atoms; two atom families with their own
 // denominators: Ex = Sx/S0c, Ey = Syo/S0c + Syb/S0t, Ez = Szo/S0c + Szb/S0t).
 #include "hipe_common.cuh"
+#include <stdio.h>
 #include <stdlib.h>
 
 namespace hipe {
@@ -682,7 +683,10 @@ static int launch(const Params& p0, const Geom& g, cudaStream_t st) {
     cfg.gridDim = dim3((unsigned)g.C, 1, 1);
     int ncl = 0;
     e = cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg);
-    if (e != cudaSuccess) { (void)cudaGetLastError(); return HIPE_E_UNSUPPORTED; }
+    if (getenv("HIPE_DEBUG"))
+        fprintf(stderr, "hipe_cluster: C=%d smem=%zu threads=%d -> cudaOccupancyMaxActiveClusters: %s, %d clusters\n",
+                g.C, smem, kThreads, cudaGetErrorString(e), ncl);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); return (int)e; }
     if (ncl < 1) return HIPE_E_UNSUPPORTED;
     if (const char* env = getenv("HIPE_CLUSTER_GRID")) {
         const int v = atoi(env);

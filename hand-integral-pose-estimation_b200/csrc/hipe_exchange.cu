@@ -47,6 +47,15 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 // grid = world CTAs: CTA p serves peer p (store + publish), waits for rank p's record, copies it out;
 // the last CTA to finish (atomic ticket) combines the `world` loss sums in rank order.  No CTA
 // waits on another CTA of this grid, so co-residency is not required for progress.
+// kPhase 0: the whole exchange in one launch (publish, wait, combine).  kPhase 1: PUBLISH only (sum,
+// stores, flag; never waits).  kPhase 2: COLLECT only (wait for the peers' flags, copy out, combine):
+// launched on a side stream one step later, it takes the rendezvous with the slowest rank off the
+// stream that runs the loss kernels -- nothing on the GPU needs the global loss value, the gradient
+// is final before the exchange.  Flow control of the split form (hipe_b200/parallel.py): a rank's
+// publish(t) is stream-ordered after its collect(t-1); so a peer that publishes t+1 into parity t-1
+// has completed collect(t), which needed this rank's publish(t), which came after this rank's
+// collect(t-1): the slot being overwritten has been read.
+template <int kPhase>
 __global__ void __launch_bounds__(kXT)
     k_peer_exchange(const double* __restrict__ loss_in, long long n_in, double in_scale, const float* __restrict__ coords,
                     long long B, int K, double* const* __restrict__ peers, int world, int rank,
@@ -63,12 +72,12 @@ __global__ void __launch_bounds__(kXT)
     const long long n = B * K;
     // 0. this rank's loss sum, in a fixed order (thread-strided partials -> warp shuffles ->
     //    kXT/32 warp partials); every CTA forms the same bits
-    {
+    if (threadIdx.x == 0) timed_out = 0;
+    if constexpr (kPhase != 2) {
         double acc = 0.0;
         for (long long i = threadIdx.x; i < n_in; i += kXT) acc += loss_in[i];
         acc = warp_sum(acc);
         if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
-        if (threadIdx.x == 0) timed_out = 0;
         __syncthreads();
         if (threadIdx.x < 32) {
             double r = warp_sum((threadIdx.x < kXT / 32) ? red[threadIdx.x] : 0.0);
@@ -77,7 +86,7 @@ __global__ void __launch_bounds__(kXT)
         __syncthreads();
     }
     // 1. my record into slot [par][rank] of peer p (16-byte stores over NVLink; own buffer when p == rank)
-    {
+    if constexpr (kPhase != 2) {
         double* dst = peers[p] + ((long long)par * world + rank) * reclen;
         if (threadIdx.x == 0) *reinterpret_cast<double2*>(dst) = make_double2(my_sum_sh, (double)B);
         const long long npair = n >> 1;
@@ -89,9 +98,14 @@ __global__ void __launch_bounds__(kXT)
     __syncthreads();
     // 2. publish to peer p, 3. wait for rank p's record in my own buffer (bounded by wall time)
     if (threadIdx.x == 0) {
-        unsigned long long* fp = reinterpret_cast<unsigned long long*>(peers[p] + 2ll * world * reclen) +
-                                 (long long)par * world + rank;
-        st_release_sys_u64(fp, seq);
+        if constexpr (kPhase != 2) {
+            unsigned long long* fp = reinterpret_cast<unsigned long long*>(peers[p] + 2ll * world * reclen) +
+                                     (long long)par * world + rank;
+            st_release_sys_u64(fp, seq);
+        }
+    }
+    if constexpr (kPhase == 1) return;
+    if (threadIdx.x == 0) {
         const unsigned long long* fm = reinterpret_cast<const unsigned long long*>(peers[rank] + 2ll * world * reclen) +
                                        (long long)par * world + p;
         const unsigned long long t0 = globaltimer_ns();
@@ -113,7 +127,11 @@ __global__ void __launch_bounds__(kXT)
         }
         if (threadIdx.x == 0) scratch[p] = ld_relaxed_sys_f64(slot);
     } else if (threadIdx.x == 0) {
-        if (err) atomicExch(err, 1u);
+        // kPhase 2: err is an array of `world` words (may be host-mapped): word p names the missing rank
+        if (err) {
+            if constexpr (kPhase == 2) *reinterpret_cast<volatile unsigned*>(err + p) = 1u;
+            else atomicExch(err, 1u);
+        }
         scratch[p] = __longlong_as_double(0x7ff8000000000000ll);
     }
     // 5. last CTA out combines in fixed rank order
@@ -162,8 +180,36 @@ extern "C" int hipe_peer_exchange(const double* loss_in, long long n_in, double 
     const long long reclen = hipe_peer_exchange_reclen(B, K);
     const unsigned long long tns = (unsigned long long)((timeout_s > 0 ? timeout_s : 20.0) * 1e9);
     // scratch: `world` doubles, then one 32-bit ticket (zero before the first launch)
-    k_peer_exchange<<<world, kXT, 0, static_cast<cudaStream_t>(stream)>>>(
+    k_peer_exchange<0><<<world, kXT, 0, static_cast<cudaStream_t>(stream)>>>(
         loss_in, n_in, in_scale, coords, B, K, reinterpret_cast<double* const*>(peers_dev), world, rank, seq, reclen,
+        value_scale, value_out, sums_out, coords_all, err, scratch, reinterpret_cast<unsigned*>(scratch + world), tns);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int hipe_peer_publish(const double* loss_in, long long n_in, double in_scale, const float* coords,
+                                 long long B, int K, void* const* peers_dev, int world, int rank,
+                                 unsigned long long seq, void* stream) {
+    if (!loss_in || !coords || !peers_dev) return HIPE_E_NULL;
+    if (world <= 0 || world > kXMaxWorld || rank < 0 || rank >= world || B <= 0 || K <= 0 || seq == 0 || n_in <= 0)
+        return HIPE_E_SHAPE;
+    const long long reclen = hipe_peer_exchange_reclen(B, K);
+    k_peer_exchange<1><<<world, kXT, 0, static_cast<cudaStream_t>(stream)>>>(
+        loss_in, n_in, in_scale, coords, B, K, reinterpret_cast<double* const*>(peers_dev), world, rank, seq, reclen,
+        0.0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0ull);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int hipe_peer_collect(void* const* peers_dev, int world, int rank, unsigned long long seq, long long B,
+                                 int K, double value_scale, double* value_out, double* sums_out,
+                                 double* coords_all, unsigned* err, double* scratch, double timeout_s,
+                                 void* stream) {
+    if (!peers_dev || !value_out || !scratch) return HIPE_E_NULL;
+    if (world <= 0 || world > kXMaxWorld || rank < 0 || rank >= world || B <= 0 || K <= 0 || seq == 0)
+        return HIPE_E_SHAPE;
+    const long long reclen = hipe_peer_exchange_reclen(B, K);
+    const unsigned long long tns = (unsigned long long)((timeout_s > 0 ? timeout_s : 20.0) * 1e9);
+    k_peer_exchange<2><<<world, kXT, 0, static_cast<cudaStream_t>(stream)>>>(
+        nullptr, 0, 0.0, nullptr, B, K, reinterpret_cast<double* const*>(peers_dev), world, rank, seq, reclen,
         value_scale, value_out, sums_out, coords_all, err, scratch, reinterpret_cast<unsigned*>(scratch + world), tns);
     return (int)cudaGetLastError();
 }

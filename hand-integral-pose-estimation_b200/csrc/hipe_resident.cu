@@ -367,6 +367,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                                : (double)reinterpret_cast<const float*>(p.vis)[it.vol * 3 + lane];
             }
             unsigned spins = 0;
+            bool gave_up = false;       // an inter-CTA wait hit its spin limit: the outputs are poisoned below
 #ifdef HIPE_RES_PROF
             RES_PROF_T0();
 #endif
@@ -396,6 +397,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                 if (HIPE_RES_POLL_NS > 0) __nanosleep(HIPE_RES_POLL_NS);
                 if (++spins > kSpinLimit) {
                     if (lane == 0) atomicExch(p.err, 1u);
+                    gave_up = true;
                     break;
                 }
             }
@@ -417,6 +419,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
                 __nanosleep(64);
                 if (++spins > kSpinLimit) {
                     if (lane == 0) atomicExch(p.err, 1u);
+                    gave_up = true;
                     break;
                 }
             }
@@ -450,15 +453,19 @@ __global__ void __launch_bounds__(kThreads, 1) k_resident(const Params p) {
             const double num_c = lane == 0 ? a[1] : (lane == 1 ? a[2] : a[3]);
             const double num_t = lane == 0 ? 0.0 : (lane == 1 ? a[5] : a[6]);
             const double dim = lane == 0 ? (double)p.W : (lane == 1 ? (double)p.H : (double)p.D);
-            const double ex_ = num_c * ic + (lane == 0 ? 0.0 : num_t * itt);
+            // A wait that gave up merged whatever was in the workspace: nothing computed from it may
+            // look valid.  NaN here poisons the coordinates, the loss term, the loss scalar and (through
+            // rec.K) every gradient element of this CTA's item of the volume.
+            const double ex_ = gave_up ? __longlong_as_double(0x7ff8000000000000ll)
+                                       : num_c * ic + (lane == 0 ? 0.0 : num_t * itt);
             const float cn = (float)(ex_ / dim - 0.5);
             // loss.py:86-89 on this volume's three coordinates, in the targets' precision
             const double dlt = (double)cn - tk;
             const double sg = (dlt > 0.0) ? 1.0 : ((dlt < 0.0) ? -1.0 : 0.0);
-            const float g1 = (float)(sg * wk * p.norm);
+            const float g1 = gave_up ? __int_as_float(0x7fc00000) : (float)(sg * wk * p.norm);
             if (lane < 3) {
-                if (it.i == 0) {
-                    if (p.loss_terms) p.loss_terms[it.vol * 3 + lane] = fabs(dlt) * wk;
+                if (it.i == 0 || gave_up) {
+                    if (p.loss_terms) p.loss_terms[it.vol * 3 + lane] = gave_up ? ex_ : fabs(dlt) * wk;
                     if (p.coords) p.coords[it.vol * 3 + lane] = cn;
                     if (p.expect) p.expect[it.vol * 3 + lane] = ex_;
                 }

@@ -48,6 +48,8 @@ SIGNATURES = {
     "hipe_peer_exchange_reclen": (_ll, [_ll, _i]),
     "hipe_peer_exchange_bytes": (_ll, [_i, _ll, _i]),
     "hipe_peer_exchange": (_i, [_vp, _ll, _d, _vp, _ll, _i, _vp, _i, _i, _c.c_ulonglong, _d, _vp, _vp, _vp, _vp, _vp, _d, _vp]),
+    "hipe_peer_publish": (_i, [_vp, _ll, _d, _vp, _ll, _i, _vp, _i, _i, _c.c_ulonglong, _vp]),
+    "hipe_peer_collect": (_i, [_vp, _i, _i, _c.c_ulonglong, _ll, _i, _d, _vp, _vp, _vp, _vp, _vp, _d, _vp]),
     "hipe_joint_location_loss_host": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp,
                                            _vp, _ll]),
     "hipe_procrustes_host": (_i, [_vp, _vp, _ll, _i, _i, _i, _vp, _vp, _vp]),

@@ -6,13 +6,25 @@ GPU 0 (main/evaluate.py:62-63, main/test.py:91-92).
 Every (sample, joint) volume and every Procrustes sample is independent, so rank r keeps the
 samples `shard_bounds(B, world, r)` -- the dim-0 chunking `scatter` does
 (balanced_parallel.py:122) -- and no volume, probability or heatmap gradient ever crosses a GPU.
-The only exchange is ONE all-gather per step of a packed record per rank,
+The only exchange per step is one packed record per rank,
 
     [ sum_r |c - gt| * vis ,  B_r ,  coords_r (B_max * 3J, zero padded) ]      (fp64)
 
 after which every rank holds all predicted joints and combines the per-replica losses in fixed
 rank order (bit-identical on every rank).  Backward needs no collective: each rank scales its own
 gradient by 1/world, exactly what `Reduce.backward` broadcasts (balanced_parallel.py:52-55).
+
+How the record travels:
+  * equal shards known a priori on CUDA (the training loop): NVLink peer memory, no NCCL launch --
+    `hipe_peer_publish` on the stream of the loss kernels (stores + flag, never waits) and
+    `hipe_peer_collect` on a side stream (waits for the peers, combines).  The main stream meets the
+    collect of step t only before the publish of step t+1, or when the loss value / the gathered
+    joints are consumed (the returned loss is a `DeferredLoss`: any use of its value first makes
+    the current stream wait for the collect), so a slow rank or a host hiccup costs the others
+    nothing until a full step later.  `defer=False` keeps the one-kernel form
+    (`hipe_peer_exchange`) in stream order.
+  * anything else (unequal / unknown shard sizes, CPU / gloo, no symmetric memory): one
+    `all_gather` of the record.
 """
 import torch
 import torch.distributed as dist
@@ -63,15 +75,63 @@ def gather_records(rec, group=None):
 class _ValueWithGradOf(torch.autograd.Function):
     """forward: `value` (a detached global loss); backward: the incoming gradient goes to `carrier`
     unchanged.  The same thing as value + (carrier - carrier.detach()) without its three launches:
-    at 0.5 ms of kernels per step the step is bound by the host's launch rate, not the GPU."""
+    at 0.5 ms of kernels per step the step is bound by the host's launch rate, not the GPU.
+    `touch=False`: return a view of `value` without launching anything on the current stream (the
+    value may still be in flight on the exchange's side stream)."""
 
     @staticmethod
-    def forward(ctx, carrier, value):
+    def forward(ctx, carrier, value, touch=True):
+        if not touch and value.dtype == carrier.dtype:
+            return value.view_as(carrier)
         return value.to(carrier.dtype).view_as(carrier).clone()
 
     @staticmethod
     def backward(ctx, g):
-        return g, None
+        return g, None, None
+
+
+# attribute reads / calls on a DeferredLoss that do not look at its value
+_NO_VALUE = frozenset(("backward", "grad_fn", "requires_grad", "is_leaf", "shape", "dtype", "device", "size", "dim",
+                       "ndim", "numel", "is_cuda", "layout", "register_hook", "retain_grad", "retains_grad",
+                       "_backward_hooks", "_version", "names", "output_nr", "_base", "is_sparse", "is_quantized",
+                       "is_meta", "is_nested", "grad", "element_size", "nelement", "ndimension", "is_contiguous",
+                       "stride", "storage_offset", "data_ptr", "__len__", "is_floating_point", "is_complex",
+                       "requires_grad_", "_is_view", "is_mkldnn", "is_xla", "is_cpu", "is_ipu", "is_xpu",
+                       "is_mps", "is_maia", "is_mtia", "is_vulkan", "is_inference", "_is_zerotensor", "is_neg",
+                       "is_conj", "get_device", "type", "untyped_storage"))
+
+
+class DeferredLoss(torch.Tensor):
+    """The loss of a sharded step whose VALUE is produced by the exchange's collect launch on a side
+    stream.  It behaves like the plain 0-dim tensor it wraps; anything that reads the value
+    (`.item()`, `.detach()`, arithmetic, printing, ...) first makes the CURRENT stream wait for the
+    collect's event -- a stream-side wait, not a host synchronisation -- while `.backward()` and
+    metadata reads do not, which is what lets the rendezvous with the slowest rank slide under the
+    next step."""
+
+    _hipe_event = None
+
+    def join(self):
+        ev = self._hipe_event
+        if ev is not None:
+            with torch._C.DisableTorchFunctionSubclass():
+                dev = torch.Tensor.device.__get__(self)
+            torch.cuda.current_stream(dev).wait_event(ev)
+        return self
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        kwargs = kwargs or {}
+        name = getattr(getattr(func, "__self__", None), "__name__", None) or getattr(func, "__name__", "")
+        if name not in _NO_VALUE:
+            for a in args:
+                if isinstance(a, DeferredLoss):
+                    a.join()
+            for a in kwargs.values():
+                if isinstance(a, DeferredLoss):
+                    a.join()
+        with torch._C.DisableTorchFunctionSubclass():
+            return func(*args, **kwargs)
 
 
 class _Exchange:
@@ -120,16 +180,19 @@ def _local_cuda_loss(heatmap_out, gt_coord, gt_vis):
 
 
 class _PeerExchange:
-    """The step's exchange as ONE kernel over NVLink peer memory (hipe_peer_exchange): every rank
-    stores its record into all peers' symmetric buffers, publishes a sequence number, waits for
-    the peers' and combines -- no NCCL launch, no stream hand-off, no pack / unpack launches.
-    The buffers come from torch.distributed._symmetric_memory (plumbing: allocation + rendezvous)."""
+    """The step's exchange over NVLink peer memory (no NCCL launch, no pack / unpack launches): every
+    rank stores its record into all peers' symmetric buffers and publishes a sequence number; a
+    collect launch waits for the peers' and combines.  `run` does both in ONE kernel in stream order
+    (hipe_peer_exchange); `run_deferred` splits them: publish on the caller's stream, collect on a
+    side stream (hipe_peer_publish / hipe_peer_collect).  The buffers come from
+    torch.distributed._symmetric_memory (plumbing: allocation + rendezvous)."""
 
-    def __init__(self, world, rank, b, k, device, group):
+    def __init__(self, world, rank, b, k, device, group, timeout_s=20.0):
         import torch.distributed._symmetric_memory as symm
         from . import _lib
         lib = _lib.load()
         self.world, self.rank, self.b, self.k, self.group = world, rank, b, k, group
+        self.timeout_s = float(timeout_s)
         nbytes = lib.hipe_peer_exchange_bytes(world, b, k)
         if nbytes <= 0:
             raise RuntimeError("peer exchange: unsupported world / shard size")
@@ -138,15 +201,23 @@ class _PeerExchange:
         self.hdl = symm.rendezvous(self.buf, dist.group.WORLD if group is None else group)
         self.peers_dev = int(self.hdl.buffer_ptrs_dev)
         self.err = torch.zeros(1, dtype=torch.int32, device=device)
+        # split form: one word per rank in pinned host memory the collect kernel writes straight into
+        # (UVA), so the host can see a timeout -- and WHICH rank is missing -- without synchronising
+        self.err_host = torch.zeros(world, dtype=torch.int32).pin_memory()
         self.scratch = torch.zeros(world + 1, dtype=torch.float64, device=device)
         self.value = torch.empty(2, dtype=torch.float64, device=device)      # alternating outputs
         self.coords_all = [torch.empty((world * b, k), dtype=torch.float64, device=device) for _ in range(2)]
         self.seq = 0
+        self.side = torch.cuda.Stream(device=device)
+        self.ev_pub = [torch.cuda.Event() for _ in range(4)]
+        self.ev_col = [torch.cuda.Event() for _ in range(4)]
+        self.last_col = None
         torch.cuda.synchronize(device)
         dist.barrier(group)                    # every buffer is zeroed before anyone's first store
 
     def run(self, loss_scalar, in_scale, coords, value_scale):
         from . import _lib, ops
+        self._join_side(coords.device)
         self.seq += 1
         slot = self.seq & 1
         out = self.value[slot:slot + 1]
@@ -156,11 +227,59 @@ class _PeerExchange:
                 loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
                 self.peers_dev,
                 self.world, self.rank, self.seq, float(value_scale), out.data_ptr(), None, call.data_ptr(),
-                self.err.data_ptr(), self.scratch.data_ptr(), 20.0, torch.cuda.current_stream(coords.device).cuda_stream))
+                self.err.data_ptr(), self.scratch.data_ptr(), self.timeout_s, torch.cuda.current_stream(coords.device).cuda_stream))
         return out.view(()), call
 
+    def _join_side(self, device):
+        if self.last_col is not None:
+            torch.cuda.current_stream(device).wait_event(self.last_col)
+            self.last_col = None
+
+    def run_deferred(self, loss_scalar, in_scale, coords, value_scale, out_dtype=torch.float64):
+        """-> (value 0-dim `out_dtype`, coords_all (world*b, k) fp64, event).  The two tensors are
+        written on the side stream; `event` fires when they are complete."""
+        from . import _lib, ops
+        lib = _lib.load()
+        dev = coords.device
+        self.check()
+        main = torch.cuda.current_stream(dev)
+        # flow control (see hipe_exchange.cu): publish(t) only after this rank's collect(t-1)
+        self._join_side(dev)
+        self.seq += 1
+        i = self.seq & 3
+        with ops._launch("peer_publish", coords):
+            _lib.check(lib.hipe_peer_publish(
+                loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
+                self.peers_dev, self.world, self.rank, self.seq, main.cuda_stream))
+        self.ev_pub[i].record(main)
+        value = torch.empty((), dtype=torch.float64, device=dev)
+        call = torch.empty((self.world * self.b, self.k), dtype=torch.float64, device=dev)
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(self.ev_pub[i])
+            with ops._launch("peer_collect", coords):
+                _lib.check(lib.hipe_peer_collect(
+                    self.peers_dev, self.world, self.rank, self.seq, self.b, self.k, float(value_scale),
+                    value.data_ptr(), None, call.data_ptr(), self.err_host.data_ptr(), self.scratch.data_ptr(),
+                    self.timeout_s, self.side.cuda_stream))
+            out = value if out_dtype == torch.float64 else value.to(out_dtype)
+            self.ev_col[i].record(self.side)
+        for t in (value, call, out):
+            t.record_stream(self.side)
+        self.last_col = self.ev_col[i]
+        return out, call, self.ev_col[i]
+
+    def check(self):
+        """Raise if an earlier collect gave up waiting (no synchronisation: the kernel writes the
+        words into pinned host memory)."""
+        if bool(self.err_host.any()):
+            missing = [r for r in range(self.world) if int(self.err_host[r]) != 0]
+            raise RuntimeError("hipe_b200 peer exchange: rank(s) %s did not publish their record within %.0f s "
+                               "(a rank skipped a step, crashed or is stalled); the global loss of that step is NaN"
+                               % (missing, self.timeout_s))
+
     def timed_out(self):
-        return bool(self.err.item() != 0)
+        torch.cuda.synchronize(self.buf.device)
+        return bool(self.err.item() != 0) or bool(self.err_host.any())
 
 
 def _peer_exchange_wanted(group, device):
@@ -204,16 +323,21 @@ def _fused_plan(heatmap_out, gt_coord):
 class ShardedJointLocationLoss(nn.Module):
     """JointLocationLoss over a batch sharded across the ranks of `group`.
 
-        crit = ShardedJointLocationLoss()
+        crit = ShardedJointLocationLoss(global_batch=B)
         loss = crit(heatmap_local, gt_local, vis_local)     # same value on every rank
         loss.backward()                                      # local kernels only
         crit.coords                                          # (B_global, 3J) on every rank
 
     `local_fn(heatmap, gt, vis) -> (loss_sum, coords)` is the per-rank computation; the default
     runs the sm_100a kernels.  (The CPU tests inject an oracle-backed function to exercise the
-    exchange logic over gloo.)"""
+    exchange logic over gloo.)
 
-    def __init__(self, group=None, local_fn=None, global_batch=None):
+    `defer` (peer-memory exchange only): True (default) = publish on the caller's stream, collect on
+    a side stream, the returned loss a `DeferredLoss`; False = the whole exchange as one kernel in
+    stream order.  `timeout_s`: how long a collect waits for a missing rank before it gives up,
+    poisons the loss with NaN and records the rank; the next `forward` (or `check()`) raises."""
+
+    def __init__(self, group=None, local_fn=None, global_batch=None, defer=True, timeout_s=20.0):
         """`global_batch`: total rows over all ranks, when every rank holds its `shard_bounds`
         share; the exchange then needs no size negotiation and no host synchronisation."""
         super().__init__()
@@ -221,53 +345,67 @@ class ShardedJointLocationLoss(nn.Module):
         self.group = group
         self.local_fn = local_fn or _local_cuda_loss
         self.global_batch = global_batch
+        self.defer = defer
+        self.timeout_s = timeout_s
         self._coords = None
         self._coords64 = None
+        self._coords_event = None
         self._xch = None
-        self._peer = None            # None = not tried yet, False = unavailable (NCCL is used)
+        self._peers = {}             # (world, b, k) -> _PeerExchange: train / val / last short batch each keep theirs
+        self._peer_off = False       # True = unavailable on this box (NCCL is used)
+        self._peer = None            # the exchange object the last step used
         self.exchange = None         # "peer" | "nccl": what the last step used
 
     def _peer_exchange(self, world, b, k, device):
         """The peer-memory exchange object for this geometry, or None.  Every rank must reach the same
         decision: success is agreed on with one MIN all-reduce at set-up time."""
-        if self._peer is False:
+        if self._peer_off:
             return None
-        p = self._peer
-        if p is not None and (p.world, p.b, p.k) == (world, b, k):
+        p = self._peers.get((world, b, k))
+        if p is not None:
             return p
         if not _peer_exchange_wanted(self.group, device):
-            self._peer = False
+            self._peer_off = True
             return None
         ok, obj = 1, None
         try:
-            obj = _PeerExchange(world, dist.get_rank(self.group), b, k, device, self.group)
+            obj = _PeerExchange(world, dist.get_rank(self.group), b, k, device, self.group, self.timeout_s)
         except Exception as e:                           # no symmetric memory / P2P on this box
             ok, self._peer_error = 0, repr(e)
         t = torch.tensor([ok], dtype=torch.int32, device=device)
         dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
         if int(t.item()) == 0:
-            self._peer = False
+            self._peer_off = True
             return None
-        self._peer = obj
+        self._peers[(world, b, k)] = obj
         return obj
+
+    def check(self):
+        """Raise if a peer-memory exchange of an earlier step timed out (names the missing ranks)."""
+        for p in self._peers.values():
+            p.check()
 
     @property
     def coords(self):
         """(B_global, 3J) predicted joints of ALL ranks, in the local coordinates' dtype (converted
-        from the fp64 exchange record on first access)."""
+        from the fp64 exchange record on first access; the current stream first waits for the
+        collect launch that produces them)."""
         if self._coords is None and self._coords64 is not None:
             c64, dt = self._coords64
+            if self._coords_event is not None:
+                torch.cuda.current_stream(c64.device).wait_event(self._coords_event)
             self._coords = c64.reshape(-1, c64.shape[-1]).to(dt)
         return self._coords
 
     @coords.setter
     def coords(self, v):
-        self._coords, self._coords64 = v, None
+        self._coords, self._coords64, self._coords_event = v, None, None
 
     def forward(self, heatmap_out, gt_coord, gt_vis):
         world = dist.get_world_size(self.group)
         counts = None
         scaled = terms = None
+        px = None
         if self.global_batch is not None:
             counts = [hi - lo for lo, hi in (shard_bounds(self.global_batch, world, r) for r in range(world))]
             b_local = heatmap_out.shape[0]
@@ -299,17 +437,23 @@ class ShardedJointLocationLoss(nn.Module):
         if counts is not None and b_local > 0 and all(c == b_local for c in counts):
             # fast path: equal shards known a priori (the training loop's case)
             denom = float(world * b_local if self.size_average else world)
-            px = self._peer_exchange(world, b_local, k, coords.device) if coords.is_cuda and \
-                coords.dtype == torch.float32 and self.local_fn is _local_cuda_loss else None
+            if px is None and coords.is_cuda and coords.dtype == torch.float32 and self.local_fn is _local_cuda_loss:
+                px = self._peer_exchange(world, b_local, k, coords.device)
+            event = None
             with torch.no_grad():
                 if px is not None:
-                    # one kernel over NVLink peer memory: (sum the loss terms,) store to all peers,
-                    # flag, wait, combine
+                    # NVLink peer memory: (sum the loss terms,) store to all peers, flag; wait, combine
                     src = terms if terms is not None else loss_sum.detach()
                     if src.dtype != torch.float64:
                         src = src.to(torch.float64)
-                    value, allc = px.run(src.reshape(-1), 1.0, coords.detach().contiguous(), 1.0 / denom)
+                    carrier_dtype = scaled.dtype if scaled is not None else loss_sum.dtype
+                    if self.defer:
+                        value, allc, event = px.run_deferred(src.reshape(-1), 1.0, coords.detach().contiguous(),
+                                                             1.0 / denom, carrier_dtype)
+                    else:
+                        value, allc = px.run(src.reshape(-1), 1.0, coords.detach().contiguous(), 1.0 / denom)
                     self.exchange = "peer"
+                    self._peer = px
                 else:
                     x = self._xch
                     if x is None or (x.world, x.b, x.k) != (world, b_local, k) or x.send.device != coords.device:
@@ -320,10 +464,17 @@ class ShardedJointLocationLoss(nn.Module):
                     value = sums.sum() / denom
                     self.exchange = "nccl"
             self._coords, self._coords64 = None, (allc.reshape(world, b_local, k), coords.dtype)
+            self._coords_event = event
             if scaled is not None:
-                return _ValueWithGradOf.apply(scaled, value)
-            own = loss_sum / b_local if self.size_average else loss_sum
-            return _ValueWithGradOf.apply(own / world, value)
+                carrier = scaled
+            else:
+                own = loss_sum / b_local if self.size_average else loss_sum
+                carrier = own / world
+            out = _ValueWithGradOf.apply(carrier, value, event is None)
+            if event is not None:
+                out = out.as_subclass(DeferredLoss)
+                out._hipe_event = event
+            return out
         with torch.no_grad():
             recs = gather_records(pack_record(loss_sum.detach(), coords.detach(), b_max), self.group)
             sums, counts, allc = unpack_records(recs, k, counts)

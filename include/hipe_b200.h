@@ -297,6 +297,24 @@ HIPE_API int hipe_peer_exchange(const double* loss_in_dev, long long n_in, doubl
                        void* stream);
 
 /*
+ * The same exchange split in two launches, so that the rendezvous with the slowest rank leaves the
+ * stream that runs the loss kernels:
+ *   hipe_peer_publish  sums the loss terms, stores this rank's record into every peer's buffer and
+ *                      publishes `seq`; never waits.
+ *   hipe_peer_collect  waits for every peer's `seq` (bounded), copies the records out and combines
+ *                      them exactly like hipe_peer_exchange; the caller launches it on a side stream.
+ *                      err_dev: `world` words (device or host-mapped memory), word p set to 1 if
+ *                      rank p did not arrive in time (value_out is then NaN).
+ * Required ordering on each rank: publish(seq) is stream-ordered after collect(seq - 1).
+ */
+HIPE_API int hipe_peer_publish(const double* loss_in_dev, long long n_in, double in_scale, const float* coords_dev,
+                      long long B, int K, void* const* peers_dev, int world, int rank, unsigned long long seq,
+                      void* stream);
+HIPE_API int hipe_peer_collect(void* const* peers_dev, int world, int rank, unsigned long long seq, long long B, int K,
+                      double value_scale, double* value_out_dev, double* sums_out_dev, double* coords_all_dev,
+                      unsigned* err_dev, double* scratch_dev, double timeout_s, void* stream);
+
+/*
  * Host-buffer convenience entry points (synchronous).
  * hipe_joint_location_loss_host: JointLocationLoss forward (+ backward when dlogits_host or
  * dlogits_dev is non-NULL) on host logits, streamed to the current device in chunks of

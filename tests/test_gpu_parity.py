@@ -131,12 +131,12 @@ def test_joint_location_loss_module(fused, tgt, geom):
     assert abs(loss.item() - ref_loss) <= 1e-5 * abs(ref_loss)
     loss.backward()
     d = x.grad.cpu().numpy().astype(np.float64).reshape(B * J, -1)
-    r = ref_g.reshape(B * J, -1)
-    # sign(c - gt) may legitimately differ where |c - gt| is below the coordinate tolerance
-    c_close = (np.abs(ref_c - gt.astype(np.float64)) < 1e-5).reshape(B * J, 3).any(axis=1)
-    scale = np.abs(r).max(axis=1, keepdims=True)
-    ok = (np.abs(d - r) <= 1e-5 * scale + 1e-12).all(axis=1) | c_close
-    assert ok.all()
+    # only an axis whose sign(c - gt) is undecidable takes our sign; the rest of the volume is checked
+    from tests import parity
+    with torch.no_grad():
+        ours_c = L.softmax_integral_tensor(x.detach(), J, W, H, D).view(B * J, 3).cpu().numpy()
+    parity.check_volumes(hm.astype(np.float64).reshape(B * J, D, H, W), gt.reshape(B * J, 3), vis.reshape(B * J, 3),
+                         1.0 / B, ours_c, None, d)
 
 
 def test_upstream_gradient_scaling_fused_and_unfused():
@@ -212,10 +212,11 @@ def test_bf16_module_default_plan_vs_oracle(geom):
     want = torch.as_tensor(refg).to(torch.bfloat16).float().numpy().reshape(B * J, -1)
     assert x.grad.dtype == torch.bfloat16
     got = x.grad.float().cpu().numpy().reshape(B * J, -1)
-    ulp = np.maximum(np.abs(want), 1e-30) * 2.0 ** -7
-    c_close = (np.abs(ref_c - gt) < 1e-5).reshape(B * J, 3).any(axis=1)   # sign(c - gt) undecidable there
-    ok = (np.abs(got - want) <= ulp + 1e-12).all(axis=1) | c_close
-    assert ok.all()
+    from tests import parity
+    with torch.no_grad():
+        ours_c = L.softmax_integral_tensor(xb, J, W, H, D).view(B * J, 3).cpu().numpy()
+    parity.check_volumes(up.reshape(B * J, D, H, W), gt.reshape(B * J, 3), vis.reshape(B * J, 3), 1.0 / B,
+                         ours_c, None, got, bf16=True)
 
 
 def test_plain_expectations_and_volume_softmax():

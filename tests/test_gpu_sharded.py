@@ -37,6 +37,12 @@ def _worker(rank, world, port, B, out_dir, geom):
             vals.append(l2.item())
         peer_used = crit.exchange
         peer_err = bool(crit._peer.timed_out()) if crit._peer else False
+        # the one-kernel, in-stream form of the same exchange (defer=False)
+        crit_s = PL.ShardedJointLocationLoss(global_batch=B, defer=False)
+        x4 = torch.as_tensor(hm[lo:hi]).cuda().requires_grad_(True)
+        l4 = crit_s(x4, torch.as_tensor(gt[lo:hi]).cuda(), torch.as_tensor(vis[lo:hi]).cuda())
+        l4.backward()
+        deferred_type = type(loss).__name__
         os.environ["HIPE_EXCHANGE"] = "nccl"
         crit_n = PL.ShardedJointLocationLoss(global_batch=B)
         x3 = torch.as_tensor(hm[lo:hi]).cuda().requires_grad_(True)
@@ -50,6 +56,8 @@ def _worker(rank, world, port, B, out_dir, geom):
                  grad=x.grad.cpu().numpy(), pa=pa.item(), raw=raw.item(), repeats=np.array(vals),
                  exchange=np.array(peer_used), exchange_n=np.array(crit_n.exchange), peer_err=np.array(peer_err),
                  loss_n=l3.item(), coords_n=crit_n.coords.cpu().numpy(), grad_n=x3.grad.cpu().numpy(),
+                 loss_s=l4.item(), coords_s=crit_s.coords.cpu().numpy(), grad_s=x4.grad.cpu().numpy(),
+                 exchange_s=np.array(crit_s.exchange), loss_type=np.array(deferred_type), loss_s_type=np.array(type(l4).__name__),
                  peer_error=np.array(getattr(crit, "_peer_error", "")))
     finally:
         dist.destroy_process_group()
@@ -79,6 +87,12 @@ def test_sharded_criterion_nccl_world2(tmp_path, geom):
         assert str(o["exchange_n"]) == "nccl" and not bool(o["peer_err"])
         assert (o["repeats"] == o["loss"]).all()
         assert abs(o["loss_n"] - o["loss"]) <= 1e-14 * abs(o["loss"])
+        # deferred (publish + side-stream collect) and in-stream forms of the peer exchange: same bits
+        if str(o["exchange"]) == "peer":
+            assert str(o["loss_type"]) == "DeferredLoss" and str(o["loss_s_type"]) == "Tensor" and str(o["exchange_s"]) == "peer"
+        assert o["loss_s"] == o["loss"]
+        np.testing.assert_array_equal(o["coords_s"], o["coords"])
+        np.testing.assert_array_equal(o["grad_s"], o["grad"])
         np.testing.assert_array_equal(o["coords_n"], o["coords"])
         np.testing.assert_array_equal(o["grad_n"], o["grad"])
     assert abs(outs[0]["loss"] - ref_loss) <= 1e-5 * ref_loss
