@@ -118,6 +118,7 @@ __device__ __forceinline__ void team_barrier() {
 // mbarrier waits that trap instead of hanging the GPU if the pipeline logic is ever wrong
 __device__ __forceinline__ void wait_cta(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
+#pragma unroll 1
     for (unsigned spin = 0; spin < (1u << 26); ++spin) {
         asm volatile(
             "{\n"
@@ -134,6 +135,7 @@ __device__ __forceinline__ void wait_cta(uint32_t bar, uint32_t parity) {
 }
 __device__ __forceinline__ void wait_cluster(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
+#pragma unroll 1
     for (unsigned spin = 0; spin < (1u << 26); ++spin) {
         asm volatile(
             "{\n"

@@ -26,6 +26,7 @@ KERNEL_EVENTS = None
 
 class _launch:
     """Counts one kernel launch; with KERNEL_EVENTS set, brackets it with events on `stream`."""
+    __slots__ = ("name", "tensor", "ev")
 
     def __init__(self, name, tensor):
         self.name, self.tensor = name, tensor
@@ -161,6 +162,9 @@ def volume_entropy(logits, n_vol, D, H, W, stats=None):
 
 
 def _targets(coords, gt, vis):
+    if (gt.dtype is vis.dtype and gt.dtype in _TGT and gt.device == coords.device and vis.device == coords.device
+            and gt.is_contiguous() and vis.is_contiguous()):
+        return gt, vis, _TGT[gt.dtype], gt.dtype          # the training loop's case: nothing to convert
     tdt = torch.promote_types(gt.dtype, vis.dtype)
     if tdt not in _TGT:
         tdt = torch.float64 if tdt == torch.float64 else torch.float32
@@ -233,14 +237,25 @@ def _fused_plan(logits, n_vol, D, H, W):
 
 
 _WORKSPACES = {}             # (device index, stream) -> uint8 scratch tensor, grown on demand
+_NEED = {}                   # (kind, dtype code, n_vol, D, H, W) -> workspace bytes (0 = unsupported)
+
+
+def _need_bytes(kind, code, n_vol, D, H, W):
+    key = (kind, code, n_vol, D, H, W)
+    v = _NEED.get(key)
+    if v is None:
+        lib = _lib.load()
+        fn = lib.hipe_resident_workspace_bytes if kind == "resident" else lib.hipe_cluster_workspace_bytes
+        v = _NEED[key] = int(fn(code, n_vol, D, H, W))
+    return v
 
 
 def resident_supported(logits, n_vol, D, H, W):
-    return _lib.load().hipe_resident_workspace_bytes(_logits_code(logits), n_vol, D, H, W) > 0
+    return _need_bytes("resident", _logits_code(logits), n_vol, D, H, W) > 0
 
 
-def _workspace(dev, nbytes):
-    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+def _workspace(dev, stream_handle, nbytes):
+    key = (dev.index, stream_handle)
     ws = _WORKSPACES.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty((nbytes + 255) // 256 * 256, dtype=torch.uint8, device=dev)
@@ -250,44 +265,13 @@ def _workspace(dev, nbytes):
 
 def resident_timed_out(device, n_vol):
     """True if an inter-CTA wait of the last resident launch on this device/stream hit its spin
-    limit (word [n_vol] of the workspace).  Synchronises; for tests and diagnostics."""
+    limit (word [n_vol] of the workspace; its outputs are NaN then).  Synchronises; for tests and
+    diagnostics."""
     dev = torch.device(device)
     ws = _WORKSPACES.get((dev.index, torch.cuda.current_stream(dev).cuda_stream))
     if ws is None:
         return False
     return bool(ws[4 * n_vol:4 * n_vol + 4].view(torch.int32).item() == 1)
-
-
-def joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm, loss_out=None):
-    """hipe_joint_loss_resident: same outputs as joint_loss_fused, each volume read from HBM once.
-    `loss_out`: optional 0-dim fp64 CUDA tensor that receives norm * sum(loss terms) from the same
-    launch (the last CTA to finish sums them)."""
-    _need_cuda(logits, "heatmaps")
-    code = _logits_code(logits)
-    if not logits.is_contiguous():
-        logits = logits.contiguous()
-    dev = logits.device
-    lib = _lib.load()
-    need = lib.hipe_resident_workspace_bytes(code, n_vol, D, H, W)
-    if need <= 0:
-        raise _lib.HipeError("libhipe_b200: error %d: geometry not supported by the resident launch"
-                             % _lib.E_UNSUPPORTED)
-    coords = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
-    gt, vis, tcode, _ = _targets(coords, gt, vis)
-    if gt.numel() != n_vol * 3 or vis.numel() != n_vol * 3:
-        raise ValueError("targets must hold 3 values per volume")
-    expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev)
-    stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
-    terms = torch.empty((n_vol * 3,), dtype=torch.float64, device=dev)
-    dlogits = torch.empty_like(logits)
-    with _on(dev):
-        ws = _workspace(dev, need)
-        with _launch("joint_loss_resident", logits):
-            check(lib.hipe_joint_loss_resident(
-                logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
-                coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), _ptr(loss_out),
-                dlogits.data_ptr(), ws.data_ptr(), ws.numel(), _stream(logits)))
-    return coords, expect, stats, terms, dlogits
 
 
 def cluster_plan(logits, n_vol, D, H, W):
@@ -304,50 +288,66 @@ def cluster_supported(logits, n_vol, D, H, W):
     return _lib.load().hipe_cluster_workspace_bytes(_logits_code(logits), n_vol, D, H, W) > 0
 
 
-def joint_loss_cluster(logits, n_vol, D, H, W, gt, vis, norm, loss_out=None):
-    """hipe_joint_loss_cluster: same outputs as joint_loss_fused; each volume lives in the shared
-    memory of one thread-block cluster between the reduction and the gradient write."""
+def _single_launch(kind, logits, n_vol, D, H, W, gt, vis, norm, loss_out, want_aux):
+    """hipe_joint_loss_cluster / hipe_joint_loss_resident.  want_aux=False leaves `expect` and `stats`
+    unallocated (the kernels take NULL): the autograd path needs neither."""
     _need_cuda(logits, "heatmaps")
     code = _logits_code(logits)
     if not logits.is_contiguous():
         logits = logits.contiguous()
     dev = logits.device
     lib = _lib.load()
-    need = lib.hipe_cluster_workspace_bytes(code, n_vol, D, H, W)
+    need = _need_bytes(kind, code, n_vol, D, H, W)
     if need <= 0:
-        raise _lib.HipeError("libhipe_b200: error %d: geometry not supported by the cluster launch"
-                             % _lib.E_UNSUPPORTED)
+        raise _lib.HipeError("libhipe_b200: error %d: geometry not supported by the %s launch"
+                             % (_lib.E_UNSUPPORTED, kind))
     coords = torch.empty((n_vol, 3), dtype=torch.float32, device=dev)
     gt, vis, tcode, _ = _targets(coords, gt, vis)
     if gt.numel() != n_vol * 3 or vis.numel() != n_vol * 3:
         raise ValueError("targets must hold 3 values per volume")
-    expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev)
-    stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
+    expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev) if want_aux else None
+    stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev) if want_aux else None
     terms = torch.empty((n_vol * 3,), dtype=torch.float64, device=dev)
     dlogits = torch.empty_like(logits)
+    fn = lib.hipe_joint_loss_cluster if kind == "cluster" else lib.hipe_joint_loss_resident
     with _on(dev):
-        ws = _workspace(dev, need)
-        with _launch("joint_loss_cluster", logits):
-            check(lib.hipe_joint_loss_cluster(
-                logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
-                coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), _ptr(loss_out),
-                dlogits.data_ptr(), ws.data_ptr(), ws.numel(), _stream(logits)))
+        st = torch.cuda.current_stream(dev).cuda_stream
+        ws = _workspace(dev, st, need)
+        with _launch("joint_loss_" + kind, logits):
+            check(fn(logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
+                     coords.data_ptr(), _ptr(expect), _ptr(stats), terms.data_ptr(), _ptr(loss_out),
+                     dlogits.data_ptr(), ws.data_ptr(), ws.numel(), st))
     return coords, expect, stats, terms, dlogits
 
 
-def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, variant=None, mode=None, loss_out=None):
+def joint_loss_cluster(logits, n_vol, D, H, W, gt, vis, norm, loss_out=None, want_aux=True):
+    """hipe_joint_loss_cluster: same outputs as joint_loss_fused; each volume lives in the shared
+    memory of one thread-block cluster between the reduction and the gradient write.
+    `loss_out`: optional 0-dim fp64 CUDA tensor that receives norm * sum(loss terms) from the same
+    launch (the last cluster to finish sums them)."""
+    return _single_launch("cluster", logits, n_vol, D, H, W, gt, vis, norm, loss_out, want_aux)
+
+
+def joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm, loss_out=None, want_aux=True):
+    """hipe_joint_loss_resident: same outputs as joint_loss_fused, each volume read from HBM once
+    (second read served by the L2 inside a bounded window).  `loss_out` as for joint_loss_cluster."""
+    return _single_launch("resident", logits, n_vol, D, H, W, gt, vis, norm, loss_out, want_aux)
+
+
+def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, variant=None, mode=None, loss_out=None,
+                     want_aux=True):
     """One launch: coords, expect, stats, per-coordinate loss terms (n_vol*3 fp64), dlogits.
-    `loss_out` (0-dim fp64 CUDA tensor, optional) is filled with the loss scalar: by the resident
-    launch itself, else by hipe_sum_f64."""
+    `loss_out` (0-dim fp64 CUDA tensor, optional) is filled with the loss scalar: by the cluster /
+    resident launch itself, else by hipe_sum_f64.  mode: None = FUSED_MODE; "auto" = fused_plan's
+    choice; "cluster" | "resident" | "stream" force a launch."""
     _need_cuda(logits, "heatmaps")
     mode = FUSED_MODE if mode is None else mode
-    if mode == "cluster" or (mode == "auto" and cluster is None and variant is None
-                             and fused_plan(logits, n_vol, D, H, W) == "cluster"):
-        return joint_loss_cluster(logits, n_vol, D, H, W, gt, vis, norm, loss_out)
-    if mode == "resident" or (mode == "auto" and cluster is None and variant is None
-                              and fused_plan(logits, n_vol, D, H, W) == "resident"):
+    plan = fused_plan(logits, n_vol, D, H, W) if (mode == "auto" and cluster is None and variant is None) else None
+    if mode == "cluster" or plan == "cluster":
+        return joint_loss_cluster(logits, n_vol, D, H, W, gt, vis, norm, loss_out, want_aux)
+    if mode == "resident" or plan == "resident":
         try:
-            return joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm, loss_out)
+            return joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm, loss_out, want_aux)
         except _lib.HipeError as e:
             if mode == "resident" or "error %d:" % _lib.E_UNSUPPORTED not in str(e):
                 raise
@@ -359,20 +359,21 @@ def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, varian
     gt, vis, tcode, _ = _targets(coords, gt, vis)
     if gt.numel() != n_vol * 3 or vis.numel() != n_vol * 3:
         raise ValueError("targets must hold 3 values per volume")
-    expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev)
-    stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev)
+    expect = torch.empty((n_vol, 3), dtype=torch.float64, device=dev) if want_aux else None
+    stats = torch.empty((n_vol, 2), dtype=torch.float32, device=dev) if want_aux else None
     terms = torch.empty((n_vol * 3,), dtype=torch.float64, device=dev)
     dlogits = torch.empty_like(logits)
-    with _on(dev), _launch("joint_loss_fused", logits):
-        check(_lib.load().hipe_joint_loss_fused(
-            logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
-            coords.data_ptr(), expect.data_ptr(), stats.data_ptr(), terms.data_ptr(), dlogits.data_ptr(),
-            DEFAULT_CLUSTER if cluster is None else cluster,
-            DEFAULT_VARIANT if variant is None else variant, _stream(logits)))
-    if loss_out is not None:
-        with _on(dev), _launch("sum_f64", terms):
-            check(_lib.load().hipe_sum_f64(terms.data_ptr(), terms.numel(), float(norm), loss_out.data_ptr(),
-                                           _stream(terms)))
+    with _on(dev):
+        st = torch.cuda.current_stream(dev).cuda_stream
+        with _launch("joint_loss_fused", logits):
+            check(_lib.load().hipe_joint_loss_fused(
+                logits.data_ptr(), code, n_vol, D, H, W, gt.data_ptr(), vis.data_ptr(), tcode, float(norm),
+                coords.data_ptr(), _ptr(expect), _ptr(stats), terms.data_ptr(), dlogits.data_ptr(),
+                DEFAULT_CLUSTER if cluster is None else cluster,
+                DEFAULT_VARIANT if variant is None else variant, st))
+        if loss_out is not None:
+            with _launch("sum_f64", terms):
+                check(_lib.load().hipe_sum_f64(terms.data_ptr(), terms.numel(), float(norm), loss_out.data_ptr(), st))
     return coords, expect, stats, terms, dlogits
 
 
@@ -551,7 +552,7 @@ class FusedJointLossFunction(torch.autograd.Function):
         out_dtype = torch.promote_types(torch.float32, torch.promote_types(gt.dtype, vis.dtype))
         loss64 = torch.empty((), dtype=torch.float64, device=heatmap_out.device)
         coords, _, _, terms, dlogits = joint_loss_fused(heatmap_out, n_vol, D, H, W, gt, vis, norm,
-                                                        loss_out=loss64 if reduce_loss else None)
+                                                        loss_out=loss64 if reduce_loss else None, want_aux=False)
         loss = loss64 if out_dtype == torch.float64 else loss64.to(out_dtype)
         ctx.dlogits = dlogits                    # not save_for_backward: it is mutated, once, by backward
         ctx.in_shape = heatmap_out.shape

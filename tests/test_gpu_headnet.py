@@ -141,3 +141,24 @@ def test_scaled_loss_and_repeated_backward():
     loss, coords, terms = ops.FusedJointLossFunction.apply(hm, gt.cuda(), vis.cuda(), J, D, D, D, 1.0 / B)
     assert loss.requires_grad and not coords.requires_grad and not terms.requires_grad
     assert coords.shape == (B, 3 * J)
+
+
+def test_graphed_step_matches_eager():
+    """hipe_b200.graphed: the captured step replays bit-identically to the eager one, on new inputs
+    copied into its static buffers, for a two-launch and a single-launch geometry."""
+    import hipe_b200
+    from nets import loss as L
+    from tests import synth
+    for D in (16, 32):
+        B = 4
+        hm = [torch.as_tensor(synth.heatmaps(B, J, D, D, D, "peaked", seed=s)).cuda() for s in (1, 2)]
+        gt, vis = (torch.as_tensor(a).cuda() for a in synth.targets(B, J, seed=3, zero_vis_frac=0.1))
+        crit = L.JointLocationLoss()
+        step = hipe_b200.graphed(crit, hm[0], gt, vis)
+        for x in (hm[1], hm[0], hm[1]):
+            xe = x.clone().requires_grad_(True)
+            le = crit(xe, gt, vis)
+            le.backward()
+            lg, gg = step(x)
+            assert lg.item() == le.item()
+            assert torch.equal(gg, xe.grad)
