@@ -57,6 +57,10 @@ constexpr int kNSums = 7;             // S0c Sx Syo Szo S0t Syb Szb
 constexpr int kNB = 4;                // scalar records in flight (merge warp -> write team)
 constexpr int kPB = 2;                // team partials in flight (reduce team -> merge warp)
 constexpr int kThreads = 2 * kC + 64; // two teams + producer warp + merge warp
+// 18 warps = 5 on the fullest scheduler partition, each partition has 16384 registers: 5 * 32 * regs
+// must stay <= 16384, i.e. <= 102 registers per thread (112 makes the launch impossible: the
+// occupancy query answers 0 clusters)
+constexpr int kMaxRegs = 96;
 constexpr float kLazy = 16.f;         // lazy re-basing threshold of the online softmax
 constexpr int kSmemMax = 232448;      // 227 KB: the opt-in dynamic shared memory of one CTA
 constexpr int kMinSpare = 3;          // slots beyond one share the ring must have (look-ahead)
@@ -78,6 +82,10 @@ struct Params {
     int slot_bytes;   // stage_bytes rounded up to 128
     int n_clusters;
     int st_hint;      // gradient stores carry an L2 evict_first hint
+    int stasync;      // partial exchange by st.async + transaction bytes (1) or plain stores + remote arrives (0)
+    double inv_W, inv_H, inv_D;
+    int hoist;        // H | SR: every stage starts at row y = 0 (row term = per-volume part + per-stage part)
+    int poly;         // 2-byte logits: gradient-pass exponentials on the FMA pipe: 0 none, 1 every other visit, 2 all
     // outputs (nullable except out)
     float* coords;
     double* expect;
@@ -95,7 +103,10 @@ struct Params {
 struct Scal {
     double E[3];              // Ex, Ey, Ez
     double K[3];              // g_a / dim_a / L per axis
+    double term[3];           // |c_a - gt_a| * vis_a
+    float cn[3];              // normalised coordinates
     float M;                  // volume maximum
+    float L;                  // sum of exponentials relative to M
     float pad;
 };
 
@@ -110,10 +121,59 @@ struct Smem {
     Scal scal[kNB];
 };
 
-template <int kId>
-__device__ __forceinline__ void team_barrier() {
-    asm volatile("bar.sync %0, %1;" ::"n"(kId), "n"(kC) : "memory");
-}
+// Wait-time profile (diagnostic builds only, -DHIPE_CLU_PROF; scripts/diag_cluster_waits.py): lane 0
+// of every warp adds the clock cycles it spent in each class of wait, and its total run time, to a
+// global table.
+//   0 producer: empty slot      1 reduce: stage landed (full)   2 reduce: red_free
+//   3 merge: red_ready          4 merge: peers' partials        5 merge: scal_free
+//   6 write: scal_ready         7 write: full (already landed)
+//   8 producer total   9 reduce total   10 merge total   11 write total   (warp-cycles)
+constexpr int kProfN = 12;
+#ifdef HIPE_CLU_PROF
+__device__ unsigned long long g_prof[kProfN];
+// per-warp register accumulators (three wait classes per role at most), flushed once at role exit:
+// an atomic per wait would itself become the bottleneck
+// event trace of CTA 0 for volumes kTraceK0 .. kTraceK0+7 (clock64 of one SM):
+//   0 first stage issued   1 last stage issued   2 last stage landed (reduce warp 0)   3 fold handed over
+//   4 merge: team partial seen   5 merge: published   6 merge: peers seen   7 merge: record ready
+//   8 write warp 0: record seen (write starts)   9 write warp 0: last stage stored
+constexpr int kTraceK0 = 24, kTraceN = 8, kTraceE = 10;
+__device__ long long g_trace[kTraceN][kTraceE];
+#define CLU_TRACE(k, ev)                                                                               \
+    do {                                                                                               \
+        if (blockIdx.x == 0 && (k) >= kTraceK0 && (k) < kTraceK0 + kTraceN && (threadIdx.x & 31) == 0)  \
+            g_trace[(k) - kTraceK0][ev] = clock64();                                                   \
+    } while (0)
+#define CLU_SLOT(cls) ((cls) == 0 || (cls) == 1 || (cls) == 3 || (cls) == 6 ? 0 : ((cls) == 5 ? 2 : 1))
+#define CLU_WAIT(cls, call)                                          \
+    do {                                                             \
+        const long long t0_ = clock64();                             \
+        call;                                                        \
+        prof_acc_[CLU_SLOT(cls)] += (unsigned long long)(clock64() - t0_); \
+    } while (0)
+#define CLU_TOTAL(role, c0, c1, c2)                                                             \
+    do {                                                                                        \
+        if ((threadIdx.x & 31) == 0) {                                                          \
+            atomicAdd(&g_prof[role], (unsigned long long)(clock64() - prof_start_));            \
+            if ((c0) >= 0) atomicAdd(&g_prof[(c0) < 0 ? 0 : (c0)], prof_acc_[0]);               \
+            if ((c1) >= 0) atomicAdd(&g_prof[(c1) < 0 ? 0 : (c1)], prof_acc_[1]);               \
+            if ((c2) >= 0) atomicAdd(&g_prof[(c2) < 0 ? 0 : (c2)], prof_acc_[2]);               \
+        }                                                                                       \
+    } while (0)
+#else
+#define CLU_WAIT(cls, call) call
+#define CLU_TOTAL(role, c0, c1, c2) do { } while (0)
+#define CLU_TRACE(k, ev) do { } while (0)
+#endif
+
+// How long one try_wait may keep the warp suspended before it returns false (ns): a waiting warp
+// then re-issues its poll loop that rarely instead of competing for issue slots with the working
+// teams (ncu on the first version: 40 % of all executed instructions were poll loops).  The wake-up
+// on completion is immediate either way.
+#ifndef HIPE_CLU_SUSPEND_NS
+#define HIPE_CLU_SUSPEND_NS 20000
+#endif
+constexpr uint32_t kSuspendNs = HIPE_CLU_SUSPEND_NS;
 
 // mbarrier waits that trap instead of hanging the GPU if the pipeline logic is ever wrong
 __device__ __forceinline__ void wait_cta(uint32_t bar, uint32_t parity) {
@@ -123,11 +183,11 @@ __device__ __forceinline__ void wait_cta(uint32_t bar, uint32_t parity) {
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
             "selp.u32 %0, 1, 0, p;\n"
             "}\n"
             : "=r"(done)
-            : "r"(bar), "r"(parity)
+            : "r"(bar), "r"(parity), "r"(kSuspendNs)
             : "memory");
         if (done) return;
     }
@@ -140,11 +200,11 @@ __device__ __forceinline__ void wait_cluster(uint32_t bar, uint32_t parity) {
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n"
             "selp.u32 %0, 1, 0, p;\n"
             "}\n"
             : "=r"(done)
-            : "r"(bar), "r"(parity)
+            : "r"(bar), "r"(parity), "r"(kSuspendNs)
             : "memory");
         if (done) return;
     }
@@ -158,10 +218,21 @@ __device__ __forceinline__ uint32_t mapa(uint32_t local_saddr, uint32_t rank) {
 __device__ __forceinline__ void st_cluster_f64(uint32_t remote_saddr, double v) {
     asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(remote_saddr), "d"(v) : "memory");
 }
+// 8-byte store into a peer's shared memory that completes 8 bytes of the peer's mbarrier transaction
+// count: data and signal travel together through the async proxy, no fence on the sender
+__device__ __forceinline__ void st_async_f64(uint32_t remote_saddr, double v, uint32_t remote_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(remote_saddr),
+                 "l"(__double_as_longlong(v)), "r"(remote_bar)
+                 : "memory");
+}
 // arrive on the mbarrier at the same offset in CTA `rank`; releases this thread's earlier
 // st.shared::cluster stores at cluster scope
 __device__ __forceinline__ void arrive_remote(uint32_t remote_bar) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote_bar) : "memory");
+}
+
+__device__ __forceinline__ __nv_bfloat162 u32_as_bf162(uint32_t w) {
+    return *reinterpret_cast<__nv_bfloat162*>(&w);
 }
 
 __device__ __forceinline__ float rebase_w(float m_from, float m_to) {
@@ -169,27 +240,89 @@ __device__ __forceinline__ float rebase_w(float m_from, float m_to) {
     return (m_from == kNegInf) ? 0.f : ex2(__fsub_rn(__fmul_rn(m_from, kLog2e), __fmul_rn(m_to, kLog2e)));
 }
 
+// 2^a for a <= ~0 on the FMA / ALU pipes instead of the quarter-rate XU (MUFU.EX2): round-to-nearest
+// split a = n + f through the 1.5 * 2^23 constant, a degree-4 minimax polynomial for 2^f on
+// [-0.5, 0.5] (relative error 2.7e-6, far below the bf16 output's 2^-9 rounding) in packed FFMA2,
+// and n added straight into the exponent field.  Used for a share of the bf16 gradient pass, whose
+// two exponentials per 2 bytes of traffic otherwise keep the XU pipe ~80 % busy at HBM speed.
+__device__ __forceinline__ float2 ex2_poly2(float2 a) {
+    a.x = fmaxf(a.x, -125.f);
+    a.y = fmaxf(a.y, -125.f);
+    const float2 magic = make_float2(12582912.f, 12582912.f), nmagic = make_float2(-12582912.f, -12582912.f);
+    const float2 t = __fadd2_rn(a, magic);
+    const float2 nf = __fadd2_rn(t, nmagic);
+    const float2 f = __ffma2_rn(nf, make_float2(-1.f, -1.f), a);
+    float2 q = __ffma2_rn(f, make_float2(0.009570102207362652f, 0.009570102207362652f),
+                          make_float2(0.05591785907745361f, 0.05591785907745361f));
+    q = __ffma2_rn(q, f, make_float2(0.240247443318367f, 0.240247443318367f));
+    q = __ffma2_rn(q, f, make_float2(0.6931217908859253f, 0.6931217908859253f));
+    q = __ffma2_rn(q, f, make_float2(0.9999992847442627f, 0.9999992847442627f));
+    return make_float2(__int_as_float(__float_as_int(q.x) + (__float_as_int(t.x) << 23)),
+                       __int_as_float(__float_as_int(q.y) + (__float_as_int(t.y) << 23)));
+}
+
 // ring position of a role: slot index and the parity of the slot's current use
 struct Ring {
     int slot;
     uint32_t lap;
-    __device__ __forceinline__ void init() { slot = 0; lap = 0; }
-    __device__ __forceinline__ void next(int nslots) {
-        if (++slot == nslots) { slot = 0; ++lap; }
+    uint32_t off;      // slot * slot_bytes
+    __device__ __forceinline__ void init() { slot = 0; lap = 0; off = 0; }
+    __device__ __forceinline__ void next(int nslots, int slot_bytes) {
+        off += (uint32_t)slot_bytes;
+        if (++slot == nslots) { slot = 0; off = 0; ++lap; }
     }
 };
+
+// fp32 >= 0 (normal or zero) -> fp64 without the conversion unit (F2F.F64.F32 shares the quarter-rate
+// XU pipe with MUFU.EX2): re-bias the exponent with integer ops.  0 maps to 2^-127 (5.9e-39), far
+// below one ulp of any sum that contains the volume maximum's e = 1; denormals cannot occur
+// (ex2.ftz flushes them).  Same helper as hipe_stream_kernel.cuh.
+__device__ __forceinline__ double widen_nonneg(float f) {
+    const uint32_t b = __float_as_uint(f);
+    return __hiloint2double((int)((b >> 3) + 0x38000000u), (int)(b << 29));
+}
+
+// Sum 8 doubles per lane over the 32 lanes of a warp with 9 double-shuffles instead of 40: each
+// step a lane hands the half of its values it will not keep to its partner.  On return every lane
+// holds the warp total of value number (lane >> 2) & 7.  Fixed order: bit-reproducible.
+__device__ __forceinline__ double warp_sum8(const double (&v)[8], int lane) {
+    double w[4], u[2];
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const double mine = b4 ? v[i + 4] : v[i], other = b4 ? v[i] : v[i + 4];
+        w[i] = mine + __shfl_xor_sync(0xffffffffu, other, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const double mine = b3 ? w[i + 2] : w[i], other = b3 ? w[i] : w[i + 2];
+        u[i] = mine + __shfl_xor_sync(0xffffffffu, other, 8);
+    }
+    double t = (b2 ? u[1] : u[0]) + __shfl_xor_sync(0xffffffffu, b2 ? u[0] : u[1], 4);
+    t += __shfl_xor_sync(0xffffffffu, t, 2);
+    t += __shfl_xor_sync(0xffffffffu, t, 1);
+    return t;
+}
 
 // Thread roles inside the CTA (kThreads = 2*kC + 64):
 //   [0, kC)          REDUCE team
 //   [kC, 2kC)        WRITE team
 //   warp 2kC/32      producer (one elected lane)
 //   warp 2kC/32 + 1  merge warp
-template <typename T>
-__global__ void __maxnreg__(112) k_cluster(const Params p) {
+// kFix: the geometry every headline shape has (64^3 fp32 and bf16, 32^3): all 256 team threads
+// active, 4096-byte visits, 16 KB stages = slots, and every stage starting at y = 0 (H | SR) -- the
+// byte offsets become immediates and the row bookkeeping collapses.  The launch is instruction-bound
+// (one CTA per SM, every role a dependency chain), so the instructions per stage are what is tuned.
+template <typename T, bool kFix>
+__global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
     using V16 = Vec16<T>;
     constexpr int VEC = V16::N;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem& sm = *reinterpret_cast<Smem*>(smem_raw + (size_t)p.nslots * p.slot_bytes);
+    const int pass_bytes = kFix ? 4096 : p.pass_bytes;
+    const int stage_bytes = kFix ? 16384 : p.stage_bytes;
+    const int slot_bytes = kFix ? 16384 : p.slot_bytes;
+    const bool hoist = kFix ? true : (p.hoist != 0);       // H | SR: every stage starts at row y = 0
+    Smem& sm = *reinterpret_cast<Smem*>(smem_raw + (size_t)p.nslots * slot_bytes);
     const uint32_t ring = smem_u32(smem_raw);
 
     const uint32_t C = cluster_nctarank();
@@ -215,18 +348,27 @@ __global__ void __maxnreg__(112) k_cluster(const Params p) {
             mbar_init(smem_u32(&sm.scal_ready[s]), 1);
             mbar_init(smem_u32(&sm.scal_free[s]), kNW);
         }
-        mbar_init(smem_u32(&sm.xfull[0]), C);
-        mbar_init(smem_u32(&sm.xfull[1]), C);
+        // st.async exchange: one local arrive.expect_tx per volume, the peers' stores complete the bytes;
+        // plain-store exchange: one remote arrive per peer
+        mbar_init(smem_u32(&sm.xfull[0]), p.stasync ? 1 : C);
+        mbar_init(smem_u32(&sm.xfull[1]), p.stasync ? 1 : C);
         mbar_fence_init();
         fence_proxy_async();
     }
     __syncthreads();
     // every CTA's barriers exist before any peer arrives on them
     cluster_sync_all();
+#ifdef HIPE_CLU_PROF
+    const long long prof_start_ = clock64();
+    unsigned long long prof_acc_[3] = {0ull, 0ull, 0ull};
+#endif
 
     if (threadIdx.x >= 2 * kC + 32) {
         // ------------------------------- merge warp -------------------------------
+        // Lane l (< 7) owns sum number l through both merges, lane 7 the maximum: every merge is a short
+        // sequential sum in a fixed order per lane (no shuffle trees on this warp's critical path).
         const int lane = threadIdx.x & 31;
+        const int li = lane < kNSums ? lane : kNSums - 1;       // the word this lane reads
         for (long long k = 0; k < nv; ++k) {
             const long long vol = cluster_id + k * p.n_clusters;
             const unsigned sb = (unsigned)(k % kPB), xb = (unsigned)(k & 1), rb = (unsigned)(k % kNB);
@@ -238,100 +380,85 @@ __global__ void __maxnreg__(112) k_cluster(const Params p) {
                 wk = p.tgt_f64 ? reinterpret_cast<const double*>(p.vis)[vol * 3 + lane]
                                : (double)reinterpret_cast<const float*>(p.vis)[vol * 3 + lane];
             }
-            // ---- this CTA's partial: merge the reduce team's warp partials ----
-            wait_cta(smem_u32(&sm.red_ready[sb]), (uint32_t)(k / kPB) & 1);
-            const float pm = (lane < kNW) ? sm.wmax[sb][lane] : kNegInf;
-            double a[kNSums];
+            if (p.stasync && lane == 0) mbar_arrive_expect_tx(smem_u32(&sm.xfull[xb]), C * 8u * (kNSums + 1));
+            // ---- this CTA's partial: the reduce team's kNW warp partials, in warp order ----
+            CLU_WAIT(3, wait_cta(smem_u32(&sm.red_ready[sb]), (uint32_t)(k / kPB) & 1));
+            CLU_TRACE(k, 4);
+            float wmx[kNW];
+            double wv[kNW];
 #pragma unroll
-            for (int i = 0; i < kNSums; ++i) a[i] = (lane < kNW) ? sm.wred[sb][lane][i] : 0.0;
+            for (int w = 0; w < kNW; ++w) {
+                wmx[w] = sm.wmax[sb][w];
+                wv[w] = sm.wred[sb][w][li];
+            }
             {
                 // hand the buffer back only once the loads above have returned (see
                 // mbar_arrive_after_loads; a warp's scoreboard covers all its lanes)
-                uint32_t dep = __float_as_uint(pm);
+                uint32_t dep = 0;
 #pragma unroll
-                for (int i = 0; i < kNSums; ++i) dep ^= (uint32_t)__double2loint(a[i]);
+                for (int w = 0; w < kNW; ++w) dep ^= __float_as_uint(wmx[w]) ^ (uint32_t)__double2loint(wv[w]);
                 __syncwarp();
                 if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.red_free[sb]), dep);
             }
-            float cm = pm;
+            float cm = wmx[0];
 #pragma unroll
-            for (int o = kNW / 2; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
-            const double f2 = (double)rebase_w(pm, cm);
+            for (int w = 1; w < kNW; ++w) cm = fmaxf(cm, wmx[w]);
+            double mine = 0.0;
 #pragma unroll
-            for (int i = 0; i < kNSums; ++i) {
-                a[i] *= f2;
-#pragma unroll
-                for (int o = kNW / 2; o > 0; o >>= 1) a[i] += __shfl_xor_sync(0xffffffffu, a[i], o);
+            for (int w = 0; w < kNW; ++w) mine = fma((double)rebase_w(wmx[w], cm), wv[w], mine);
+            if (lane == kNSums) mine = (double)cm;
+            // ---- publish to every CTA of the cluster (self included): lane l stores word l ----
+            if (p.stasync) {
+                if (lane <= kNSums) {
+                    const uint32_t src = smem_u32(&sm.xch[xb][crank][lane]), bar = smem_u32(&sm.xfull[xb]);
+                    for (uint32_t r = 0; r < C; ++r) st_async_f64(mapa(src, r), mine, mapa(bar, r));
+                }
+            } else {
+                if (lane <= kNSums) {
+                    const uint32_t src = smem_u32(&sm.xch[xb][crank][lane]);
+                    for (uint32_t r = 0; r < C; ++r) st_cluster_f64(mapa(src, r), mine);
+                }
+                __syncwarp();       // the arriving lanes' release covers the other lanes' stores
+                if (lane < (int)C) arrive_remote(mapa(smem_u32(&sm.xfull[xb]), (uint32_t)lane));
             }
-            // lanes 0..7 now all hold the CTA's sums; broadcast lane 0's copy to the whole warp
-            cm = __shfl_sync(0xffffffffu, cm, 0);
-#pragma unroll
-            for (int i = 0; i < kNSums; ++i) a[i] = __shfl_sync(0xffffffffu, a[i], 0);
-            // ---- publish to every CTA of the cluster (self included), lane r -> rank r ----
-            if (lane < (int)C) {
-                const uint32_t dst = mapa(smem_u32(&sm.xch[xb][crank][0]), (uint32_t)lane);
-#pragma unroll
-                for (int i = 0; i < kNSums; ++i) st_cluster_f64(dst + 8u * i, a[i]);
-                st_cluster_f64(dst + 56u, (double)cm);
-                arrive_remote(mapa(smem_u32(&sm.xfull[xb]), (uint32_t)lane));
-            }
+            CLU_TRACE(k, 5);
             // ---- all C partials of this volume, merged in rank order ----
-            wait_cluster(smem_u32(&sm.xfull[xb]), (uint32_t)(k >> 1) & 1);
-            double b[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) b[i] = (lane < (int)C) ? sm.xch[xb][lane][i] : 0.0;
-            const float mi = (lane < (int)C) ? (float)b[7] : kNegInf;
-            const float M = warp_max(mi);
-            const double fr = (double)rebase_w(mi, M);
-#pragma unroll
-            for (int i = 0; i < kNSums; ++i) a[i] = warp_sum(b[i] * fr);
+            CLU_WAIT(4, wait_cluster(smem_u32(&sm.xfull[xb]), (uint32_t)(k >> 1) & 1));
+            CLU_TRACE(k, 6);
+            float M = kNegInf;
+            for (uint32_t r = 0; r < C; ++r) M = fmaxf(M, (float)sm.xch[xb][r][kNSums]);
+            double a = 0.0;
+            for (uint32_t r = 0; r < C; ++r)
+                a = fma((double)rebase_w((float)sm.xch[xb][r][kNSums], M), sm.xch[xb][r][li], a);
             // loss.py:39-41 (expectations) and :54-56 (normalisation), in fp64, rounded once.
-            // Lane a (< 3) finishes axis a: x, y, z.
-            const double ic = 1.0 / a[0], itt = 1.0 / a[4];
-            const double num_c = lane == 0 ? a[1] : (lane == 1 ? a[2] : a[3]);
-            const double num_t = lane == 0 ? 0.0 : (lane == 1 ? a[5] : a[6]);
-            const double dim = lane == 0 ? (double)p.W : (lane == 1 ? (double)p.H : (double)p.D);
+            // Lane t (< 3) finishes axis t: x, y, z.  Sums: 0 S0c 1 Sx 2 Syo 3 Szo 4 S0t 5 Syb 6 Szb.
+            const double a0 = __shfl_sync(0xffffffffu, a, 0), a4 = __shfl_sync(0xffffffffu, a, 4);
+            const double num_c = __shfl_sync(0xffffffffu, a, (lane < 3) ? 1 + lane : lane);
+            const double num_t = __shfl_sync(0xffffffffu, a, (lane == 1 || lane == 2) ? 4 + lane : lane);
+            const double ic = 1.0 / a0, itt = 1.0 / a4;
+            const double inv_dim = lane == 0 ? p.inv_W : (lane == 1 ? p.inv_H : p.inv_D);
             const double ex_ = num_c * ic + (lane == 0 ? 0.0 : num_t * itt);
-            const float cn = (float)(ex_ / dim - 0.5);
+            const float cn = (float)(ex_ * inv_dim - 0.5);
             // loss.py:86-89 on this volume's three coordinates, in the targets' precision
             const double dlt = (double)cn - tk;
             const double sg = (dlt > 0.0) ? 1.0 : ((dlt < 0.0) ? -1.0 : 0.0);
             const float g1 = (float)(sg * wk * p.norm);
-            if (k >= kNB) wait_cta(smem_u32(&sm.scal_free[rb]), (uint32_t)((k / kNB) - 1) & 1);
+            if (k >= kNB) CLU_WAIT(5, wait_cta(smem_u32(&sm.scal_free[rb]), (uint32_t)((k / kNB) - 1) & 1));
             Scal& rec = sm.scal[rb];
             if (lane < 3) {
-                if (crank == 0) {
-                    if (p.loss_terms) p.loss_terms[vol * 3 + lane] = fabs(dlt) * wk;
-                    if (p.coords) p.coords[vol * 3 + lane] = cn;
-                    if (p.expect) p.expect[vol * 3 + lane] = ex_;
-                }
                 rec.E[lane] = ex_;
-                rec.K[lane] = (double)g1 / dim * ic;     // g_a / dim_a / L
+                rec.K[lane] = (double)g1 * inv_dim * ic;     // g_a / dim_a / L
+                rec.term[lane] = fabs(dlt) * wk;
+                rec.cn[lane] = cn;
             }
-            if (lane == 0) {
-                rec.M = M;
-                if (crank == 0 && p.stats) { p.stats[vol * 2 + 0] = M; p.stats[vol * 2 + 1] = (float)a[0]; }
-            }
+            if (lane == 0) { rec.M = M; rec.L = (float)a0; }
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(&sm.scal_ready[rb]));
+            CLU_TRACE(k, 7);
+            // (the volume's outputs go to global memory from the write team: a global store here would
+            // sit in front of this warp's next cluster-scope release and stall it)
         }
-        // The loss scalar without a second launch: rank 0's merge warps are the writers of
-        // loss_terms, so the last of them to finish sums the terms (fixed order: lane-strided
-        // partials, then the shuffle tree) -- loss.py:88-89.
-        if (crank == 0 && p.loss_out && p.loss_terms) {
-            __threadfence();
-            __syncwarp();
-            unsigned t = 0;
-            if (lane == 0) t = atomicAdd(p.ticket, 1u);
-            t = __shfl_sync(0xffffffffu, t, 0);
-            if (t == (unsigned)p.n_clusters - 1) {
-                __threadfence();
-                double acc = 0.0;
-                for (long long i = lane; i < p.n_vol * 3; i += 32) acc += __ldcg(p.loss_terms + i);
-                acc = warp_sum(acc);
-                if (lane == 0) p.loss_out[0] = acc * p.norm;
-            }
-        }
+        CLU_TOTAL(10, 3, 4, 5);
         return;
     }
 
@@ -343,35 +470,30 @@ __global__ void __maxnreg__(112) k_cluster(const Params p) {
             r.init();
             for (long long k = 0; k < nv; ++k) {
                 const long long vol = cluster_id + k * p.n_clusters;
-                const unsigned char* src = p.in + vol * p.vol_bytes + (long long)sv0 * p.stage_bytes;
+                const unsigned char* src = p.in + vol * p.vol_bytes + (long long)sv0 * stage_bytes;
                 for (int s = 0; s < nst; ++s) {
-                    if (r.lap > 0) wait_cta(smem_u32(&sm.empty[r.slot]), (r.lap - 1) & 1);
+                    if (r.lap > 0) CLU_WAIT(0, wait_cta(smem_u32(&sm.empty[r.slot]), (r.lap - 1) & 1));
+                    if (s == 0) CLU_TRACE(k, 0);
+                    if (s == nst - 1) CLU_TRACE(k, 1);
                     const uint32_t bar = smem_u32(&sm.full[r.slot]);
-                    mbar_arrive_expect_tx(bar, (uint32_t)p.stage_bytes);
-                    tma_load_1d(ring + (uint32_t)r.slot * (uint32_t)p.slot_bytes, src + (long long)s * p.stage_bytes,
-                                (uint32_t)p.stage_bytes, bar, pol);
-                    r.next(p.nslots);
+                    mbar_arrive_expect_tx(bar, (uint32_t)stage_bytes);
+                    tma_load_1d(ring + r.off, src, (uint32_t)stage_bytes, bar, pol);
+                    src += stage_bytes;
+                    r.next(p.nslots, slot_bytes);
                 }
             }
         }
+        CLU_TOTAL(8, 0, -1, -1);
         return;
     }
 
     const bool is_writer = threadIdx.x >= kC;
     const int tid = is_writer ? threadIdx.x - kC : threadIdx.x;   // team-local
     const int lane = tid & 31, warp = tid >> 5;
-    const bool active = tid < p.nact;
+    const bool active = kFix ? true : (tid < p.nact);
     const int cg = active ? tid % p.G : 0;
     const int rr = active ? tid / p.G : 0;
     const int x0 = cg * VEC;
-    // row offsets of this thread's kKP visits inside a stage
-    int yo[kKP], zo[kKP];
-#pragma unroll
-    for (int q = 0; q < kKP; ++q) {
-        const int rho = rr + q * p.R;
-        zo[q] = rho / p.H;
-        yo[q] = rho - zo[q] * p.H;
-    }
     const int rowbase0 = sv0 * p.SR;              // first row of the share
     const int zb0 = rowbase0 / p.H, yb0 = rowbase0 - zb0 * p.H;
     const uint32_t lds_base = ring + 16u * tid;
@@ -380,6 +502,7 @@ __global__ void __maxnreg__(112) k_cluster(const Params p) {
         // =============================== REDUCE team ===============================
         Ring r;
         r.init();
+        const double dzd = (double)(p.SR / p.H);      // hoist: z advance per stage
         for (long long k = 0; k < nv; ++k) {
             const unsigned sb = (unsigned)(k % kPB);
             float m = kNegInf, mL = kNegInf, tm = kNegInf;   // offset in use, fl(m*log2e), true maximum
@@ -389,30 +512,40 @@ __global__ void __maxnreg__(112) k_cluster(const Params p) {
 #pragma unroll
                 for (int j = 0; j < VEC / 2; ++j) c2[q][j] = make_float2(0.f, 0.f);
             double s0t = 0.0, syb = 0.0, szb = 0.0;
-            int zb = zb0, yb = yb0;
+            int zb = zb0, yb = yb0;                 // general geometry
+            double zbd = (double)zb0;               // hoist: the stage's first z as a double, y is 0
             auto fetch = [&](uint4 (&dst)[kKP]) {
-                wait_cta(smem_u32(&sm.full[r.slot]), r.lap & 1);
+                CLU_WAIT(1, wait_cta(smem_u32(&sm.full[r.slot]), r.lap & 1));
                 if (active) {
-                    const uint32_t sbase = lds_base + (uint32_t)r.slot * (uint32_t)p.slot_bytes;
+                    const uint32_t sbase = lds_base + r.off;
 #pragma unroll
-                    for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * p.pass_bytes);
+                    for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * pass_bytes);
                 }
-                r.next(p.nslots);
+                r.next(p.nslots, slot_bytes);
             };
             auto compute = [&](const uint4 (&raw)[kKP]) {
                 if (active) {
-                    float v[kKP][VEC];
+                    // the stage's maximum straight from the raw words (2-byte logits: packed bf16x2
+                    // maxima, half the instructions and nothing unpacked yet)
+                    float smax;
+                    if constexpr (VEC == 8) {
+                        __nv_bfloat162 mx = u32_as_bf162(raw[0].x);
 #pragma unroll
-                    for (int q = 0; q < kKP; ++q) V16::unpack(raw[q], v[q]);
-                    float smax = kNegInf;
+                        for (int q = 0; q < kKP; ++q) {
+                            mx = __hmax2(mx, __hmax2(__hmax2(u32_as_bf162(raw[q].x), u32_as_bf162(raw[q].y)),
+                                                     __hmax2(u32_as_bf162(raw[q].z), u32_as_bf162(raw[q].w))));
+                        }
+                        smax = fmaxf(__low2float(mx), __high2float(mx));
+                    } else {
+                        smax = kNegInf;
 #pragma unroll
-                    for (int q = 0; q < kKP; ++q)
-#pragma unroll
-                        for (int j = 0; j < VEC; ++j) smax = fmaxf(smax, v[q][j]);
+                        for (int q = 0; q < kKP; ++q)
+                            smax = fmaxf(smax, fmaxf(fmaxf(__uint_as_float(raw[q].x), __uint_as_float(raw[q].y)),
+                                                     fmaxf(__uint_as_float(raw[q].z), __uint_as_float(raw[q].w))));
+                    }
                     tm = fmaxf(tm, smax);
                     // LAZY re-basing: the offset m only moves when a value exceeds it by more than
-                    // kLazy (e <= exp(kLazy) ~ 9e6 stays far inside fp32); the fold re-bases once,
-                    // onto the thread's true maximum tm.
+                    // kLazy (e <= exp(kLazy) ~ 9e6 stays far inside fp32); the fold re-bases once.
                     if (smax > m + kLazy) {
                         const float f = rebase_w(m, smax);
                         const float2 f2 = make_float2(f, f);
@@ -428,29 +561,38 @@ __global__ void __maxnreg__(112) k_cluster(const Params p) {
                     // all -inf so far: exponentiate against 0 so that e = 2^-inf = 0 (no NaN)
                     const float noff = (m == kNegInf) ? 0.f : -mL;
                     const float2 noff2 = make_float2(noff, noff), l2e2 = make_float2(kLog2e, kLog2e);
-                    float rowsum[kKP];
+                    float2 rs2 = make_float2(0.f, 0.f);
 #pragma unroll
                     for (int q = 0; q < kKP; ++q) {
+                        float v[VEC];
+                        V16::unpack(raw[q], v);
                         float2 e2[VEC / 2];
 #pragma unroll
                         for (int j = 0; j < VEC / 2; ++j) {
-                            const float2 a2 = __ffma2_rn(make_float2(v[q][2 * j], v[q][2 * j + 1]), l2e2, noff2);
+                            const float2 a2 = __ffma2_rn(make_float2(v[2 * j], v[2 * j + 1]), l2e2, noff2);
                             e2[j] = make_float2(ex2(a2.x), ex2(a2.y));
                             c2[q][j] = __fadd2_rn(c2[q][j], e2[j]);
                         }
                         float2 r2 = __fadd2_rn(e2[0], e2[1]);
                         if constexpr (VEC == 8) r2 = __fadd2_rn(r2, __fadd2_rn(e2[2], e2[VEC / 2 - 1]));
-                        rowsum[q] = r2.x + r2.y;
+                        rs2 = (q == 0) ? r2 : __fadd2_rn(rs2, r2);
                     }
-                    const float2 t2 = __fadd2_rn(make_float2(rowsum[0], rowsum[2]), make_float2(rowsum[1], rowsum[3]));
-                    const double dt = (double)(t2.x + t2.y);
+                    const double dt = widen_nonneg(rs2.x + rs2.y);
                     s0t += dt;
-                    syb = fma((double)yb, dt, syb);
-                    szb = fma((double)zb, dt, szb);
+                    if (hoist) {
+                        szb = fma(zbd, dt, szb);
+                    } else {
+                        syb = fma((double)yb, dt, syb);
+                        szb = fma((double)zb, dt, szb);
+                    }
                 }
                 // next stage's base row (uniform): SR | H or H | SR, so one of the two moves
-                yb += p.SR;
-                while (yb >= p.H) { yb -= p.H; ++zb; }
+                if (hoist) {
+                    zbd += dzd;
+                } else {
+                    yb += p.SR;
+                    while (yb >= p.H) { yb -= p.H; ++zb; }
+                }
             };
             // Stage s+1 is fetched into registers before the arithmetic of stage s: two stages'
             // dependency chains overlap in every warp.
@@ -473,141 +615,207 @@ __global__ void __maxnreg__(112) k_cluster(const Params p) {
                     compute(rawA);
                 }
             }
-            // ---- fold the thread's accumulators, merge over the warp, hand to the merge warp ----
-            double q7[kNSums];
+            if (warp == 0) CLU_TRACE(k, 2);
+            // ---- fold the thread's accumulators, sum over the warp, hand to the merge warp ----
+            double q8[8];
 #pragma unroll
-            for (int i = 0; i < kNSums; ++i) q7[i] = 0.0;
-            float pmx = kNegInf;
+            for (int i = 0; i < 8; ++i) q8[i] = 0.0;
             if (active) {
-                pmx = tm;
                 double col[VEC];
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) col[j] = 0.0;
 #pragma unroll
                 for (int q = 0; q < kKP; ++q) {
+                    // row offsets of this thread's visit q inside a stage
+                    const int rho = rr + q * p.R;
+                    const int zo = rho / p.H, yo = rho - zo * p.H;
                     double row = 0.0;
 #pragma unroll
                     for (int j = 0; j < VEC; ++j) {
-                        const double cd = (double)((j & 1) ? c2[q][j / 2].y : c2[q][j / 2].x);
+                        const double cd = widen_nonneg((j & 1) ? c2[q][j / 2].y : c2[q][j / 2].x);
                         row += cd;
                         col[j] += cd;
                     }
-                    q7[2] = fma((double)yo[q], row, q7[2]);
-                    q7[3] = fma((double)zo[q], row, q7[3]);
+                    q8[2] = fma((double)yo, row, q8[2]);
+                    q8[3] = fma((double)zo, row, q8[3]);
                 }
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) {
-                    q7[0] += col[j];
-                    q7[1] = fma((double)(x0 + j), col[j], q7[1]);
+                    q8[0] += col[j];
+                    q8[1] = fma((double)(x0 + j), col[j], q8[1]);
                 }
-                q7[4] = s0t; q7[5] = syb; q7[6] = szb;
-                // from the lazy offset onto the thread's true maximum (weight <= 1)
-                const double fl_ = (double)rebase_w(m, tm);
-#pragma unroll
-                for (int i = 0; i < kNSums; ++i) q7[i] *= fl_;
+                q8[4] = s0t; q8[5] = syb; q8[6] = szb;
             }
-            const float wm = warp_max(pmx);
-            const double f = (double)rebase_w(pmx, wm);
+            // from the thread's lazy offset straight onto the warp's true maximum (weight <= 1)
+            const float wm = warp_max(active ? tm : kNegInf);
+            const double f = active ? (double)rebase_w(m, wm) : 0.0;
 #pragma unroll
-            for (int i = 0; i < kNSums; ++i) q7[i] = warp_sum(q7[i] * f);
-            if (k >= kPB) wait_cta(smem_u32(&sm.red_free[sb]), (uint32_t)((k / kPB) - 1) & 1);
-            if (lane == 0) {
-#pragma unroll
-                for (int i = 0; i < kNSums; ++i) sm.wred[sb][warp][i] = q7[i];
-                sm.wmax[sb][warp] = wm;
-                mbar_arrive(smem_u32(&sm.red_ready[sb]));
-            }
+            for (int i = 0; i < kNSums; ++i) q8[i] *= f;
+            const double tot = warp_sum8(q8, lane);
+            if (k >= kPB) CLU_WAIT(2, wait_cta(smem_u32(&sm.red_free[sb]), (uint32_t)((k / kPB) - 1) & 1));
+            if ((lane & 3) == 0) sm.wred[sb][warp][lane >> 2] = tot;
+            if (lane == 0) sm.wmax[sb][warp] = wm;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&sm.red_ready[sb]));
+            if (warp == 0) CLU_TRACE(k, 3);
         }
+        CLU_TOTAL(9, 1, 2, -1);
         return;
     }
 
     // ================================ WRITE team ================================
+    // row offsets of this thread's kKP visits inside a stage, as exact small floats
     float yof[kKP], zof[kKP];
 #pragma unroll
-    for (int q = 0; q < kKP; ++q) { yof[q] = (float)yo[q]; zof[q] = (float)zo[q]; }
-    const float Hf = (float)p.H, SRf = (float)p.SR;
+    for (int q = 0; q < kKP; ++q) {
+        const int rho = rr + q * p.R;
+        const int zo = rho / p.H;
+        zof[q] = (float)zo;
+        yof[q] = (float)(rho - zo * p.H);
+    }
+    const float Hf = (float)p.H, SRf = (float)p.SR, dzf = (float)(p.SR / p.H);
     const uint64_t st_pol = policy_evict_first();
+    const float2 l2e2 = make_float2(kLog2e, kLog2e);
     Ring r;
     r.init();
     for (long long k = 0; k < nv; ++k) {
         const long long vol = cluster_id + k * p.n_clusters;
         const unsigned rb = (unsigned)(k % kNB);
-        wait_cta(smem_u32(&sm.scal_ready[rb]), (uint32_t)(k / kNB) & 1);
+        CLU_WAIT(6, wait_cta(smem_u32(&sm.scal_ready[rb]), (uint32_t)(k / kNB) & 1));
+        if (warp == 0) CLU_TRACE(k, 8);
         const Scal& rec = sm.scal[rb];
         const double kxd = rec.K[0], Ex = rec.E[0], Ey = rec.E[1], Ez = rec.E[2];
         const float ky = (float)rec.K[1], kz = (float)rec.K[2];
         const float ML = __fmul_rn(rec.M, kLog2e);
+        uint32_t dep_out = 0;
+        if (crank == 0 && warp == 0) {
+            // the volume's outputs (rank 0's first write warp: lanes 0-2 one axis each)
+            if (lane < 3) {
+                const double term = rec.term[lane], ea = rec.E[lane];
+                const float cn = rec.cn[lane];
+                dep_out = (uint32_t)__double2loint(term) ^ __float_as_uint(cn);
+                if (p.loss_terms) p.loss_terms[vol * 3 + lane] = term;
+                if (p.coords) p.coords[vol * 3 + lane] = cn;
+                if (p.expect) p.expect[vol * 3 + lane] = ea;
+            }
+            if (lane == 0 && p.stats) {
+                const float L = rec.L;
+                dep_out ^= __float_as_uint(L);
+                p.stats[vol * 2 + 0] = rec.M;
+                p.stats[vol * 2 + 1] = L;
+            }
+            dep_out = __shfl_sync(0xffffffffu, dep_out, 0) ^ __shfl_sync(0xffffffffu, dep_out, 1);
+        }
         {
             // the record slot goes back to the merge warp only once these loads have returned
             const uint32_t dep = (uint32_t)__double2loint(kxd) ^ (uint32_t)__double2loint(Ex) ^
                                  (uint32_t)__double2loint(Ey) ^ (uint32_t)__double2loint(Ez) ^
-                                 __float_as_uint(ky) ^ __float_as_uint(kz) ^ __float_as_uint(ML);
+                                 __float_as_uint(ky) ^ __float_as_uint(kz) ^ __float_as_uint(ML) ^ dep_out;
             __syncwarp();
             if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.scal_free[rb]), dep);
         }
-        const float2 nML2 = make_float2(-ML, -ML), l2e2 = make_float2(kLog2e, kLog2e);
-        float ax[VEC];
+        const float2 nML2 = make_float2(-ML, -ML);
+        float2 ax2[VEC / 2];
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) ax[j] = (float)(kxd * ((double)(x0 + j) - Ex));
+        for (int j = 0; j < VEC / 2; ++j)
+            ax2[j] = make_float2((float)(kxd * ((double)(x0 + 2 * j) - Ex)), (float)(kxd * ((double)(x0 + 2 * j + 1) - Ex)));
         // (idx - E) must keep its ABSOLUTE accuracy: E split into hi + lo floats, the row index an
         // exact small float, so (y - Eh) is exact near the peak and - El restores the rest
         const float Eyh = (float)Ey, Eyl = (float)(Ey - (double)Eyh);
         const float Ezh = (float)Ez, Ezl = (float)(Ez - (double)Ezh);
+        // hoist (every stage starts at y = 0): the visit's row term is A[q] + B(stage),
+        //   A[q] = ky (yo_q - Ey) + kz zo_q      per volume,     B = kz (z_stage - Ez)   per stage
+        float rowA[kKP];
+#pragma unroll
+        for (int q = 0; q < kKP; ++q) rowA[q] = fmaf(kz, zof[q], ky * ((yof[q] - Eyh) - Eyl));
         float ybf = (float)yb0, zbf = (float)zb0;
-        unsigned char* gdst = p.out + vol * p.vol_bytes + (long long)sv0 * p.stage_bytes + 16ll * tid;
+        unsigned char* gdst = p.out + vol * p.vol_bytes + (long long)sv0 * stage_bytes + 16ll * tid;
 
         auto fetch = [&](uint4 (&dst)[kKP]) {
             // already complete (the reduce team consumed this stage); makes the TMA's bytes
             // visible to this thread as well
-            wait_cta(smem_u32(&sm.full[r.slot]), r.lap & 1);
+            CLU_WAIT(7, wait_cta(smem_u32(&sm.full[r.slot]), r.lap & 1));
             if (active) {
-                const uint32_t sbase = lds_base + (uint32_t)r.slot * (uint32_t)p.slot_bytes;
+                const uint32_t sbase = lds_base + r.off;
 #pragma unroll
-                for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * p.pass_bytes);
+                for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * pass_bytes);
             }
             // the slot goes back to the producer only once the loads have RETURNED
             uint32_t dep = 0;
 #pragma unroll
             for (int q = 0; q < kKP; ++q) dep ^= dst[q].x;
             if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.empty[r.slot]), active ? dep : 0u);
-            r.next(p.nslots);
+            r.next(p.nslots, slot_bytes);
         };
-        auto compute = [&](const uint4 (&raw)[kKP], int s) {
+        auto compute = [&](const uint4 (&raw)[kKP]) {
             if (active) {
+                const float rowB = kz * ((zbf - Ezh) - Ezl);
 #pragma unroll
                 for (int q = 0; q < kKP; ++q) {
-                    const float y = ybf + yof[q], z = zbf + zof[q];
-                    const float rtv = fmaf(ky, (y - Eyh) - Eyl, kz * ((z - Ezh) - Ezl));
+                    float rtv;
+                    if (hoist) {
+                        rtv = rowA[q] + rowB;
+                    } else {
+                        const float y = ybf + yof[q], z = zbf + zof[q];
+                        rtv = fmaf(ky, (y - Eyh) - Eyl, kz * ((z - Ezh) - Ezl));
+                    }
                     float v[VEC], o[VEC];
                     V16::unpack(raw[q], v);
                     const float2 rt2 = make_float2(rtv, rtv);
 #pragma unroll
                     for (int j = 0; j < VEC / 2; ++j) {
                         const float2 a2 = __ffma2_rn(make_float2(v[2 * j], v[2 * j + 1]), l2e2, nML2);
-                        const float2 w2 = __fadd2_rn(make_float2(ax[2 * j], ax[2 * j + 1]), rt2);
-                        const float2 o2 = __fmul2_rn(make_float2(ex2(a2.x), ex2(a2.y)), w2);
+                        const float2 w2 = __fadd2_rn(ax2[j], rt2);
+                        float2 e2;
+                        if (VEC == 8 && (p.poly == 2 || (p.poly == 1 && (q & 1)))) e2 = ex2_poly2(a2);
+                        else e2 = make_float2(ex2(a2.x), ex2(a2.y));
+                        const float2 o2 = __fmul2_rn(e2, w2);
                         o[2 * j] = o2.x;
                         o[2 * j + 1] = o2.y;
                     }
-                    unsigned char* dst = gdst + (long long)s * p.stage_bytes + q * p.pass_bytes;
+                    unsigned char* dst = gdst + q * pass_bytes;
                     if (p.st_hint) stg_stream_hint(dst, V16::pack(o), st_pol);
                     else stg_stream(dst, V16::pack(o));
                 }
             }
-            ybf += SRf;
-            while (ybf >= Hf) { ybf -= Hf; zbf += 1.f; }
+            gdst += stage_bytes;
+            if (hoist) {
+                zbf += dzf;
+            } else {
+                ybf += SRf;
+                while (ybf >= Hf) { ybf -= Hf; zbf += 1.f; }
+            }
         };
         uint4 rawA[kKP], rawB[kKP];
         fetch(rawA);
         for (int s = 0; s < nst; s += 2) {
             if (s + 1 < nst) fetch(rawB);
-            compute(rawA, s);
+            compute(rawA);
             if (s + 1 < nst) {
                 if (s + 2 < nst) fetch(rawA);
-                compute(rawB, s + 1);
+                compute(rawB);
             }
         }
+        if (warp == 0) CLU_TRACE(k, 9);
     }
+    // The loss scalar without a second launch: rank 0's first write warps are the writers of
+    // loss_terms, so the last of them to finish sums the terms (fixed order: lane-strided partials,
+    // then the shuffle tree) -- loss.py:88-89.
+    if (crank == 0 && warp == 0 && p.loss_out && p.loss_terms) {
+        __threadfence();
+        __syncwarp();
+        unsigned t = 0;
+        if (lane == 0) t = atomicAdd(p.ticket, 1u);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t == (unsigned)p.n_clusters - 1) {
+            __threadfence();
+            double acc = 0.0;
+            for (long long i = lane; i < p.n_vol * 3; i += 32) acc += __ldcg(p.loss_terms + i);
+            acc = warp_sum(acc);
+            if (lane == 0) p.loss_out[0] = acc * p.norm;
+        }
+    }
+    CLU_TOTAL(11, 6, 7, -1);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -640,7 +848,7 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
     }
     if (!found) return false;
     g->slot_bytes = (g->stage_bytes + 127) / 128 * 128;
-    int nslots = (int)((kSmemMax - (int)sizeof(Smem) - 128) / g->slot_bytes);
+    int nslots = (int)((kSmemMax - (int)sizeof(Smem)) / g->slot_bytes);   // the ring is a multiple of 128 bytes: Smem follows it directly
     if (nslots > kMaxSlots) nslots = kMaxSlots;
     if (const char* env = getenv("HIPE_CLUSTER_SLOTS")) {
         const int v = atoi(env);
@@ -664,9 +872,9 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
     return g->C > 0;
 }
 
-template <typename T>
+template <typename T, bool kFix>
 static int launch(const Params& p0, const Geom& g, cudaStream_t st) {
-    auto kern = k_cluster<T>;
+    auto kern = k_cluster<T, kFix>;
     const size_t smem = (size_t)g.nslots * g.slot_bytes + sizeof(Smem);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -705,6 +913,22 @@ static int launch(const Params& p0, const Geom& g, cudaStream_t st) {
 }  // namespace hipe
 
 using namespace hipe;
+
+#ifdef HIPE_CLU_PROF
+// diagnostic builds only: read (and optionally clear) the wait-time table
+extern "C" __attribute__((visibility("default"))) int hipe_cluster_prof(unsigned long long* out, int reset) {
+    cudaError_t e = cudaMemcpyFromSymbol(out, clu::g_prof, sizeof(unsigned long long) * clu::kProfN);
+    if (e != cudaSuccess) return (int)e;
+    if (reset) {
+        unsigned long long z[clu::kProfN] = {};
+        e = cudaMemcpyToSymbol(clu::g_prof, z, sizeof(z));
+    }
+    return (int)e;
+}
+extern "C" __attribute__((visibility("default"))) int hipe_cluster_trace(long long* out) {
+    return (int)cudaMemcpyFromSymbol(out, clu::g_trace, sizeof(long long) * clu::kTraceN * clu::kTraceE);
+}
+#endif
 
 extern "C" long long hipe_cluster_workspace_bytes(int dtype, long long n_vol, int D, int H, int W) {
     if (dtype != HIPE_F32 && dtype != HIPE_BF16) return 0;
@@ -763,6 +987,8 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     p.nact = g.nact; p.NSv = g.NSv; p.nslots = g.nslots; p.slot_bytes = g.slot_bytes;
     p.st_hint = 0;
     if (const char* env = getenv("HIPE_ST_HINT")) p.st_hint = (env[0] != '0') ? 1 : 0;
+    p.poly = 0;
+    if (const char* env = getenv("HIPE_CLUSTER_POLY")) p.poly = (env[0] >= '0' && env[0] <= '2') ? env[0] - '0' : 0;
     p.coords = coords; p.expect = expect; p.stats = stats; p.loss_terms = loss_terms;
     p.gt = gt; p.vis = vis; p.tgt_f64 = (tgt_dtype == HIPE_F64); p.norm = norm;
     p.ticket = static_cast<unsigned*>(workspace);
@@ -771,5 +997,13 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     e = cudaMemsetAsync(workspace, 0, 256, st);
     if (e != cudaSuccess) return (int)e;
-    return dtype == HIPE_F32 ? clu::launch<float>(p, g, st) : clu::launch<__nv_bfloat16>(p, g, st);
+    p.hoist = (g.SR % H == 0) ? 1 : 0;
+    p.inv_W = 1.0 / (double)W; p.inv_H = 1.0 / (double)H; p.inv_D = 1.0 / (double)D;
+    p.stasync = 1;
+    if (const char* env = getenv("HIPE_CLUSTER_STASYNC")) p.stasync = (env[0] != '0') ? 1 : 0;
+    const bool fix = g.nact == clu::kC && g.pass_bytes == 4096 && g.stage_bytes == 16384 && g.slot_bytes == 16384 &&
+                     p.hoist && !getenv("HIPE_CLUSTER_GENERIC");
+    if (dtype == HIPE_F32)
+        return fix ? clu::launch<float, true>(p, g, st) : clu::launch<float, false>(p, g, st);
+    return fix ? clu::launch<__nv_bfloat16, true>(p, g, st) : clu::launch<__nv_bfloat16, false>(p, g, st);
 }

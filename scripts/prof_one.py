@@ -29,6 +29,8 @@ for _ in range(a.iters):
         ops.softargmax_backward(x, n, D, D, D, s, e, g, cluster=a.cluster, variant=a.variant)
     elif a.op == "resident":
         ops.joint_loss_resident(x, n, D, D, D, gt, vis, 1.0 / a.B)
+    elif a.op == "cluster":
+        ops.joint_loss_cluster(x, n, D, D, D, gt, vis, 1.0 / a.B)
     elif a.op == "fused":
         ops.joint_loss_fused(x, n, D, D, D, gt, vis, 1.0 / a.B, cluster=a.cluster, variant=a.variant)
 torch.cuda.synchronize()
