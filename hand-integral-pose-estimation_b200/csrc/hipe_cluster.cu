@@ -309,18 +309,21 @@ __device__ __forceinline__ double warp_sum8(const double (&v)[8], int lane) {
 //   [kC, 2kC)        WRITE team
 //   warp 2kC/32      producer (one elected lane)
 //   warp 2kC/32 + 1  merge warp
-// kFix: the geometry every headline shape has (64^3 fp32 and bf16, 32^3): all 256 team threads
-// active, 4096-byte visits, 16 KB stages = slots, and every stage starting at y = 0 (H | SR) -- the
-// byte offsets become immediates and the row bookkeeping collapses.  The launch is instruction-bound
-// (one CTA per SM, every role a dependency chain), so the instructions per stage are what is tuned.
-template <typename T, bool kFix>
+// kPass != 0: a geometry known at compile time -- kPass bytes per visit (= 16 bytes x active team
+// threads), stages = slots of 4 visits, every stage starting at y = 0 (H | SR): 4096 for 64^3 and
+// 32^3 (fp32 and bf16: all 256 team threads active), 3136 for 56^3 (196 threads).  The byte offsets
+// become immediates and the row bookkeeping collapses.  The launch is instruction-bound (one CTA per
+// SM, every role a dependency chain), so the instructions per stage are what is tuned.  kPass == 0
+// takes any geometry pick_geom accepts.
+template <typename T, int kPass>
 __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
     using V16 = Vec16<T>;
     constexpr int VEC = V16::N;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int pass_bytes = kFix ? 4096 : p.pass_bytes;
-    const int stage_bytes = kFix ? 16384 : p.stage_bytes;
-    const int slot_bytes = kFix ? 16384 : p.slot_bytes;
+    constexpr bool kFix = kPass != 0;
+    const int pass_bytes = kFix ? kPass : p.pass_bytes;
+    const int stage_bytes = kFix ? kKP * kPass : p.stage_bytes;
+    const int slot_bytes = kFix ? kKP * kPass : p.slot_bytes;    // both specialised sizes are multiples of 128
     const bool hoist = kFix ? true : (p.hoist != 0);       // H | SR: every stage starts at row y = 0
     Smem& sm = *reinterpret_cast<Smem*>(smem_raw + (size_t)p.nslots * slot_bytes);
     const uint32_t ring = smem_u32(smem_raw);
@@ -425,11 +428,21 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
             // ---- all C partials of this volume, merged in rank order ----
             CLU_WAIT(4, wait_cluster(smem_u32(&sm.xfull[xb]), (uint32_t)(k >> 1) & 1));
             CLU_TRACE(k, 6);
-            float M = kNegInf;
-            for (uint32_t r = 0; r < C; ++r) M = fmaxf(M, (float)sm.xch[xb][r][kNSums]);
+            // all loads first (independent), then the short dependent chains
+            float mr[kMaxCluster];
+            double vr[kMaxCluster];
+#pragma unroll
+            for (int r = 0; r < kMaxCluster; ++r) {
+                const bool on = (uint32_t)r < C;
+                mr[r] = on ? (float)sm.xch[xb][r][kNSums] : kNegInf;
+                vr[r] = on ? sm.xch[xb][r][li] : 0.0;
+            }
+            float M = mr[0];
+#pragma unroll
+            for (int r = 1; r < kMaxCluster; ++r) M = fmaxf(M, mr[r]);
             double a = 0.0;
-            for (uint32_t r = 0; r < C; ++r)
-                a = fma((double)rebase_w((float)sm.xch[xb][r][kNSums], M), sm.xch[xb][r][li], a);
+#pragma unroll
+            for (int r = 0; r < kMaxCluster; ++r) a = fma((double)rebase_w(mr[r], M), vr[r], a);
             // loss.py:39-41 (expectations) and :54-56 (normalisation), in fp64, rounded once.
             // Lane t (< 3) finishes axis t: x, y, z.  Sums: 0 S0c 1 Sx 2 Syo 3 Szo 4 S0t 5 Syb 6 Szb.
             const double a0 = __shfl_sync(0xffffffffu, a, 0), a4 = __shfl_sync(0xffffffffu, a, 4);
@@ -490,7 +503,7 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
     const bool is_writer = threadIdx.x >= kC;
     const int tid = is_writer ? threadIdx.x - kC : threadIdx.x;   // team-local
     const int lane = tid & 31, warp = tid >> 5;
-    const bool active = kFix ? true : (tid < p.nact);
+    const bool active = kFix ? (kPass / 16 >= kC || tid < kPass / 16) : (tid < p.nact);
     const int cg = active ? tid % p.G : 0;
     const int rr = active ? tid / p.G : 0;
     const int x0 = cg * VEC;
@@ -732,9 +745,10 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
         unsigned char* gdst = p.out + vol * p.vol_bytes + (long long)sv0 * stage_bytes + 16ll * tid;
 
         auto fetch = [&](uint4 (&dst)[kKP]) {
-            // already complete (the reduce team consumed this stage); makes the TMA's bytes
-            // visible to this thread as well
-            CLU_WAIT(7, wait_cta(smem_u32(&sm.full[r.slot]), r.lap & 1));
+            // The stage landed long ago: the reduce team observed its `full` barrier, and the chain
+            // reduce team -> red_ready -> merge warp -> scal_ready -> this thread (each an mbarrier
+            // release / acquire pair) orders the TMA's bytes before these loads.  Re-checking the
+            // barrier here cost 14 % of the write team's time.
             if (active) {
                 const uint32_t sbase = lds_base + r.off;
 #pragma unroll
@@ -855,26 +869,35 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
         if (v >= 2 && v < nslots) nslots = v;
     }
     g->nslots = nslots;
-    // smallest cluster whose largest share leaves kMinSpare slots of look-ahead
+    // Cluster size.  What a B200 can hold at once (cudaOccupancyMaxActiveClusters with this kernel's
+    // footprint, profiles/r2_cluster_occupancy.md): clusters of 1 / 2 CTAs reach all 148 SMs, 3 -> 135,
+    // 4 -> 132, 5 -> 130, 6 -> 132, 7 -> 105, 8 -> 120.  Among the sizes whose largest share leaves
+    // kMinSpare slots of look-ahead, take the one that keeps the most SMs busy (ties: the larger
+    // cluster, i.e. the smaller share).  Measured on 64^3: fp32 C=6 0.505 ms vs C=8 0.518, C=5 0.550,
+    // C=7 0.622; bf16 C=3 0.638 vs C=4 0.652, C=5 0.738.
+    static const int kSMs[kMaxCluster + 1] = {0, 148, 148, 135, 132, 130, 132, 105, 120};
     int want = 0;
     if (const char* env = getenv("HIPE_CLUSTER_C")) want = atoi(env);
     g->C = 0;
+    int best = -1;
     for (int C = 1; C <= kMaxCluster; ++C) {
-        if (want ? (C != want) : ((C & (C - 1)) != 0)) continue;   // auto: powers of two only
+        if (want && C != want) continue;
         if (g->NSv < C) break;
         const int share = (g->NSv + C - 1) / C;
         if (share + (want ? 1 : kMinSpare) > nslots) continue;
-        g->C = C;
-        g->max_share = share;
-        break;
+        if (kSMs[C] >= best) {
+            best = kSMs[C];
+            g->C = C;
+            g->max_share = share;
+        }
     }
     (void)n_vol;
     return g->C > 0;
 }
 
-template <typename T, bool kFix>
+template <typename T, int kPass>
 static int launch(const Params& p0, const Geom& g, cudaStream_t st) {
-    auto kern = k_cluster<T, kFix>;
+    auto kern = k_cluster<T, kPass>;
     const size_t smem = (size_t)g.nslots * g.slot_bytes + sizeof(Smem);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -1001,9 +1024,13 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     p.inv_W = 1.0 / (double)W; p.inv_H = 1.0 / (double)H; p.inv_D = 1.0 / (double)D;
     p.stasync = 1;
     if (const char* env = getenv("HIPE_CLUSTER_STASYNC")) p.stasync = (env[0] != '0') ? 1 : 0;
-    const bool fix = g.nact == clu::kC && g.pass_bytes == 4096 && g.stage_bytes == 16384 && g.slot_bytes == 16384 &&
-                     p.hoist && !getenv("HIPE_CLUSTER_GENERIC");
+    int pass = 0;      // specialised geometry?
+    if (p.hoist && g.stage_bytes == 4 * g.pass_bytes && g.slot_bytes == g.stage_bytes && g.nact * 16 == g.pass_bytes &&
+        !getenv("HIPE_CLUSTER_GENERIC"))
+        pass = (g.pass_bytes == 4096 || g.pass_bytes == 3136) ? g.pass_bytes : 0;
     if (dtype == HIPE_F32)
-        return fix ? clu::launch<float, true>(p, g, st) : clu::launch<float, false>(p, g, st);
-    return fix ? clu::launch<__nv_bfloat16, true>(p, g, st) : clu::launch<__nv_bfloat16, false>(p, g, st);
+        return pass == 4096 ? clu::launch<float, 4096>(p, g, st)
+                            : (pass == 3136 ? clu::launch<float, 3136>(p, g, st) : clu::launch<float, 0>(p, g, st));
+    return pass == 4096 ? clu::launch<__nv_bfloat16, 4096>(p, g, st)
+                        : (pass == 3136 ? clu::launch<__nv_bfloat16, 3136>(p, g, st) : clu::launch<__nv_bfloat16, 0>(p, g, st));
 }

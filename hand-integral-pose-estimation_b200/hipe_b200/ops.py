@@ -214,23 +214,33 @@ def fused_plan(logits, n_vol, D, H, W):
 
 
 def _fused_plan(logits, n_vol, D, H, W):
-    """Which launch computes loss + gradient fastest for this geometry, from B200 measurements
-    (profiles/r1_configs.md): "resident" (persistent on-chip launch, one HBM read + one write)
-    for the fp32 geometry it is tuned for -- 256-byte rows, volumes <= 1 MiB, i.e. 21x64^3;
-    "stream" (one launch, second read through L2) for every other fp32 / bf16 volume >= 128 KiB:
-    with the backwards second pass and the share-sized clusters it beats the pair at every size
-    measured (fp32 32^3 x 5376: 0.275 ms vs 0.335, 40^3 x 672: 0.082 vs 0.103, 48^3 x 2016: 0.361
-    vs 0.419, 56^3 x 672: 0.203 vs 0.232, 96^3 x 672: 0.98 vs 1.08; bf16 48^3 x 5376: 0.564 vs
-    0.626, 64^3 x 2688: 0.61 vs 0.70, 96^3 x 672: 0.59 vs 0.64); None = the two-launch forward +
-    recompute backward, which still wins on tiny volumes (fp32 16^3: 0.366 ms vs 0.433 fused;
-    bf16 32^3 is a tie)."""
+    """Which launch computes loss + gradient fastest for this geometry, from same-box B200 A/Bs
+    (profiles/r2_configs.md):
+      "cluster"  the cluster-resident launch (hipe_joint_loss_cluster: every volume held in the
+                 distributed shared memory of one thread-block cluster, one HBM read + one write,
+                 nothing in L2) for the geometries its loops are specialised for -- 4096- or
+                 3136-byte visits with every stage starting at y = 0, i.e. 64^3, 32^3 and 56^3 in
+                 fp32 and bf16: fp32 64^3 x 1344 0.495 ms vs 0.540 resident / 0.565 stream, x 672 0.265
+                 vs 0.301; bf16 64^3 x 10752 2.37 vs 2.61 stream, x 1344 0.317 vs 0.332; fp32 32^3 x
+                 5376 0.25 vs 0.278;
+      "stream"   one launch whose second read goes through L2 (hipe_joint_loss_fused) for every other
+                 fp32 / bf16 volume >= 128 KiB (fp32 48^3 x 2016: 0.362 vs 0.42 cluster, 96^3 does not
+                 fit a cluster);
+      None       the two-launch forward + recompute backward, which still wins on tiny volumes (fp32
+                 16^3: 0.366 ms vs 0.433 fused; bf16 32^3 is a tie).
+    "resident" (hipe_joint_loss_resident, the L2-window launch that was the fp32 64^3 default before
+    the cluster launch: 0.540 ms) stays reachable through FUSED_MODE / mode="resident"."""
     esz = logits.element_size()
     vol_bytes = D * H * W * esz
     if logits.dtype not in (torch.float32, torch.bfloat16):
         return None
-    if (logits.dtype == torch.float32 and W * 4 == 256 and vol_bytes <= (1 << 20) and n_vol >= 296
-            and resident_supported(logits, n_vol, D, H, W)):
-        return "resident"
+    if vol_bytes >= (1 << 17) and n_vol >= 8:
+        cp = cluster_plan(logits, n_vol, D, H, W)
+        if cp is not None:
+            stage_bytes, row_bytes = cp[3], W * esz
+            sr = stage_bytes // row_bytes                       # rows per stage
+            if stage_bytes in (16384, 12544) and sr % H == 0:   # the specialised loops
+                return "cluster"
     if (W * esz) % 16 == 0 and vol_bytes >= (1 << 17):
         return "stream"
     return None

@@ -88,15 +88,19 @@ def case(dt, D, B, envs):
 if __name__ == "__main__":
     quick = "quick" in sys.argv
     f32, bf = torch.float32, torch.bfloat16
-    case(f32, 64, 64, [{}, {"HIPE_CLUSTER_STASYNC": "0"}, {"HIPE_CLUSTER_SLOTS": "13"}, {"HIPE_CLUSTER_C": "6"},
-                       {"HIPE_CLUSTER_C": "6", "HIPE_CLUSTER_STASYNC": "0"}, {"HIPE_CLUSTER_C": "5"}, {"HIPE_CLUSTER_C": "7"}])
-    case(bf, 64, 128, [{}, {"HIPE_CLUSTER_STASYNC": "0"}, {"HIPE_CLUSTER_POLY": "1"}, {"HIPE_CLUSTER_C": "3"},
-                       {"HIPE_CLUSTER_C": "5"}, {"HIPE_CLUSTER_C": "6"}, {"HIPE_CLUSTER_C": "8"}])
+    if "56" in sys.argv:
+        case(f32, 56, 32, [{}, {"HIPE_CLUSTER_GENERIC": "1"}, {"HIPE_CLUSTER_C": "4"}, {"HIPE_CLUSTER_C": "5"}, {"HIPE_CLUSTER_C": "8"}])
+        case(f32, 56, 96, [{}, {"HIPE_CLUSTER_GENERIC": "1"}, {"HIPE_CLUSTER_C": "4"}, {"HIPE_CLUSTER_C": "5"}, {"HIPE_CLUSTER_C": "8"}])
+        case(bf, 56, 96, [{}, {"HIPE_CLUSTER_C": "3"}, {"HIPE_CLUSTER_C": "4"}])
+        case(f32, 64, 64, [{}])
+        sys.exit(0)
+    case(f32, 64, 64, [{}, {"HIPE_CLUSTER_STASYNC": "0"}, {"HIPE_CLUSTER_C": "8"}, {"HIPE_CLUSTER_C": "5"}])
+    case(bf, 64, 128, [{}, {"HIPE_CLUSTER_POLY": "1"}, {"HIPE_CLUSTER_C": "4"}])
     if not quick:
-        case(bf, 64, 512, [{}, {"HIPE_CLUSTER_POLY": "1"}, {"HIPE_CLUSTER_C": "8"}])
-        case(bf, 64, 64, [{}, {"HIPE_CLUSTER_C": "8"}])
-        case(f32, 56, 32, [{}, {"HIPE_CLUSTER_C": "8"}, {"HIPE_CLUSTER_C": "7"}])
-        case(f32, 56, 96, [{}, {"HIPE_CLUSTER_C": "8"}, {"HIPE_CLUSTER_C": "7"}])
+        case(bf, 64, 512, [{}, {"HIPE_CLUSTER_C": "4"}])
+        case(bf, 64, 64, [{}])
+        case(f32, 56, 32, [{}, {"HIPE_CLUSTER_C": "4"}, {"HIPE_CLUSTER_C": "8"}])
+        case(f32, 56, 96, [{}, {"HIPE_CLUSTER_C": "4"}, {"HIPE_CLUSTER_C": "8"}])
         case(f32, 64, 32, [{}])
-        case(f32, 48, 96, [{}, {"HIPE_CLUSTER_C": "3"}])
-        case(f32, 32, 256, [{}, {"HIPE_CLUSTER_C": "2"}])
+        case(f32, 48, 96, [{}])
+        case(f32, 32, 256, [{}, {"HIPE_CLUSTER_C": "1"}])

@@ -79,16 +79,22 @@ def test_launch_plan_host_logic():
         x = torch.empty(0, dtype=dtype)
         return ops._fused_plan(x, n_vol, d, d, d)
 
-    assert plan(torch.float32, 1344, 64) == "resident"
-    assert plan(torch.float32, 42, 64) == "stream"          # too few volumes for the persistent grid
-    assert plan(torch.float32, 2016, 56) == "stream"
-    assert plan(torch.float32, 672, 96) == "stream"
-    assert plan(torch.float32, 1344, 32) == "stream"        # 128 KB volumes
+    assert plan(torch.float32, 1344, 64) == "cluster"       # specialised loops: 4096-byte visits, H | SR
+    assert plan(torch.float32, 42, 64) == "cluster"
+    assert plan(torch.float32, 2016, 56) == "cluster"       # 3136-byte visits
+    assert plan(torch.float32, 672, 96) == "stream"         # 3.5 MB: does not fit a cluster
+    assert plan(torch.float32, 2016, 48) == "stream"        # fits, but the general loops lose to the stream launch
+    assert plan(torch.float32, 1344, 32) == "cluster"       # 128 KB volumes
     assert plan(torch.float32, 1344, 16) is None            # 16 KB volumes: forward + recompute backward
-    assert plan(torch.bfloat16, 2688, 64) == "stream"
-    assert plan(torch.bfloat16, 4032, 56) == "stream"
+    assert plan(torch.bfloat16, 2688, 64) == "cluster"
+    assert plan(torch.bfloat16, 4032, 56) == "cluster"
     assert plan(torch.bfloat16, 2688, 32) is None
     assert plan(torch.float64, 1344, 64) is None
+    # the plan query behind "cluster": cluster size, ring slots, stages per share, bytes per stage
+    assert ops.cluster_plan(torch.empty(0), 1344, 64, 64, 64) == (6, 14, 11, 16384)
+    assert ops.cluster_plan(torch.empty(0, dtype=torch.bfloat16), 1344, 64, 64, 64) == (3, 14, 11, 16384)
+    assert ops.cluster_plan(torch.empty(0), 672, 56, 56, 56)[3] == 12544
+    assert ops.cluster_plan(torch.empty(0), 672, 96, 96, 96) is None
     # the tiling query behind "resident": supported geometries report a workspace size, others 0
     lib = __import__("hipe_b200._lib", fromlist=["load"]).load()
     assert lib.hipe_resident_workspace_bytes(0, 1344, 64, 64, 64) > 0

@@ -13,21 +13,21 @@ from tests.test_gpu_resident import _check, _cuda
 
 pytestmark = pytest.mark.gpu
 
-# geometry -> cluster size the launch picks (None: the volume does not fit one cluster)
-CLU_GEOMS = {
-    (16, 16, 16): 1,
-    (32, 32, 32): 1,
-    (64, 64, 64): 8,     # headline: 1 MiB on 8 CTAs x 8 stages
-    (56, 56, 56): 4,     # reference default (main/config.py:23-25): 14 stages of 12.25 KB per CTA
-    (48, 48, 48): 4,
-    (16, 128, 64): 4,    # stage = half a z-slice (SR | H, non-zero y base)
-    (12, 20, 24): 1,     # 30 rows per visit, 180 of 256 team threads active
-}
+# geometries the launch takes (the cluster size is the library's choice: hipe_cluster_plan)
+CLU_GEOMS = [
+    (16, 16, 16),
+    (32, 32, 32),
+    (64, 64, 64),        # headline: 1 MiB over 6 CTAs x <= 11 stages
+    (56, 56, 56),        # reference default (main/config.py:23-25): 12.25 KB stages
+    (48, 48, 48),
+    (16, 128, 64),       # stage = half a z-slice (SR | H, non-zero y base: general row terms)
+    (12, 20, 24),        # 30 rows per visit, 180 of 256 team threads active
+]
 UNSUPPORTED = [(96, 96, 96), (8, 8, 8), (5, 6, 7), (3, 9, 100)]
 
 
 @pytest.mark.parametrize("regime", ["noise", "peaked", "sharp"])
-@pytest.mark.parametrize("geom", list(CLU_GEOMS))
+@pytest.mark.parametrize("geom", CLU_GEOMS)
 def test_cluster_vs_oracle(geom, regime):
     from hipe_b200 import ops
     D, H, W = geom
@@ -36,7 +36,7 @@ def test_cluster_vs_oracle(geom, regime):
     gt, vis = synth.targets(B, J, seed=11, zero_vis_frac=0.1)
     x = _cuda(hm)
     plan = ops.cluster_plan(x, B * J, D, H, W)
-    assert plan is not None and plan[0] == CLU_GEOMS[geom], plan
+    assert plan is not None and 1 <= plan[0] <= 8 and plan[2] + 3 <= plan[1], plan
     out = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
     torch.cuda.synchronize()
     worst = _check(hm, gt, vis, D, H, W, B, J, out)
@@ -74,7 +74,7 @@ def test_every_cluster_size(csize):
     _check(hm, gt, vis, D, H, W, B, J, out)
 
 
-def test_many_volumes_per_cluster_and_reproducible():
+def test_many_volumes_per_cluster_and_reproducible(monkeypatch):
     """More volumes than clusters (every role loops, ring laps and both exchange buffers are
     reused many times), a count that is not a multiple of the cluster count, bit-reproducible."""
     from hipe_b200 import ops
@@ -84,6 +84,7 @@ def test_many_volumes_per_cluster_and_reproducible():
     gt, vis = synth.targets(B, J, seed=21, zero_vis_frac=0.1)
     x = _cuda(hm)
     loss = torch.full((), float("nan"), dtype=torch.float64, device="cuda")
+    monkeypatch.setenv("HIPE_CLUSTER_C", "8")      # one cluster size for every variant below: same merge order, same bits
     out = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B, loss_out=loss)
     torch.cuda.synchronize()
     _check(hm, gt, vis, D, H, W, B, J, out)
@@ -92,7 +93,8 @@ def test_many_volumes_per_cluster_and_reproducible():
     out2 = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
     assert torch.equal(out[4], out2[4]) and torch.equal(out[0], out2[0]) and torch.equal(out[3], out2[3])
     # a small ring (3 slots of look-ahead only) and a tiny grid (one cluster walks everything)
-    for env in ({"HIPE_CLUSTER_SLOTS": "11"}, {"HIPE_CLUSTER_GRID": "1"}, {"HIPE_CLUSTER_GRID": "3"}):
+    for env in ({"HIPE_CLUSTER_SLOTS": "9"}, {"HIPE_CLUSTER_GRID": "1"}, {"HIPE_CLUSTER_GRID": "3"},
+                {"HIPE_CLUSTER_STASYNC": "0"}, {"HIPE_CLUSTER_GENERIC": "1"}):
         os.environ.update(env)
         try:
             out3 = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)

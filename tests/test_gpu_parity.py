@@ -197,13 +197,14 @@ def test_bf16_module_default_plan_vs_oracle(geom):
     xb = _cuda(hm32).to(torch.bfloat16)
     up = xb.float().cpu().numpy().astype(np.float64)
     plan = ops.fused_plan(xb, B * J, D, H, W)
-    assert plan == ("stream" if D * H * W * 2 >= (1 << 17) else None)
+    assert (plan is None) == (D * H * W * 2 < (1 << 17))
     x = xb.clone().requires_grad_(True)
     ops.KERNEL_EVENTS = {}
     try:
         loss = L.JointLocationLoss()(x, _cuda(gt), _cuda(vis))
         loss.backward()
         assert ("joint_loss_fused" in ops.KERNEL_EVENTS) == (plan == "stream")
+        assert ("joint_loss_cluster" in ops.KERNEL_EVENTS) == (plan == "cluster")
     finally:
         ops.KERNEL_EVENTS = None
     ref_loss, ref_c = O.joint_location_loss(up, gt, vis, return_coords=True)

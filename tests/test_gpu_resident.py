@@ -165,17 +165,22 @@ def test_module_uses_resident_launch_and_scales_upstream_gradient():
 
 
 def test_default_module_picks_the_measured_fastest_launch():
-    """fused=None: 21x64^3 fp32 batches go to the resident launch, other volumes >= 128 KB to the
-    streaming fused launch, smaller volumes to forward + recompute backward."""
+    """fused=None: 64^3 / 56^3 / 32^3 fp32 and bf16 64^3 / 56^3 batches go to the cluster-resident
+    launch, other volumes >= 128 KB to the streaming fused launch, smaller volumes to forward +
+    recompute backward."""
     from hipe_b200 import ops
     from nets import loss as L
     x64 = torch.empty((16, 21 * 64, 64, 64), device="cuda")
-    assert ops.fused_plan(x64, 16 * 21, 64, 64, 64) == "resident"
-    assert ops.fused_plan(x64[:2], 42, 64, 64, 64) == "stream"           # too few volumes to fill the grid
-    assert ops.fused_plan(x64.bfloat16(), 16 * 21, 64, 64, 64) == "stream"
+    assert ops.fused_plan(x64, 16 * 21, 64, 64, 64) == "cluster"
+    assert ops.fused_plan(x64[:2], 42, 64, 64, 64) == "cluster"
+    assert ops.fused_plan(x64.bfloat16(), 16 * 21, 64, 64, 64) == "cluster"
     assert ops.fused_plan(x64.bfloat16()[:, :21 * 32, :32, :32], 16 * 21, 32, 32, 32) is None
     x56 = torch.empty((2, 21 * 56, 56, 56), device="cuda")
-    assert ops.fused_plan(x56, 42, 56, 56, 56) == "stream"
+    assert ops.fused_plan(x56, 42, 56, 56, 56) == "cluster"
+    x48 = torch.empty((2, 21 * 48, 48, 48), device="cuda")
+    assert ops.fused_plan(x48, 42, 48, 48, 48) == "stream"
+    x96 = torch.empty((1, 21 * 96, 96, 96), device="cuda")
+    assert ops.fused_plan(x96, 21, 96, 96, 96) == "stream"
     x16 = torch.empty((2, 21 * 16, 16, 16), device="cuda")
     assert ops.fused_plan(x16, 42, 16, 16, 16) is None
     hm = synth.heatmaps(16, 21, 64, 64, 64, "peaked", seed=11)
@@ -185,7 +190,8 @@ def test_default_module_picks_the_measured_fastest_launch():
         x = _cuda(hm).requires_grad_(True)
         loss = L.JointLocationLoss()(x, _cuda(gt), _cuda(vis))
         loss.backward()
-        assert "joint_loss_resident" in ops.KERNEL_EVENTS and "softargmax_bwd" not in ops.KERNEL_EVENTS
+        assert "joint_loss_cluster" in ops.KERNEL_EVENTS and "softargmax_bwd" not in ops.KERNEL_EVENTS
+        assert "sum_f64" not in ops.KERNEL_EVENTS            # the launch writes the loss scalar itself
     finally:
         ops.KERNEL_EVENTS = None
     y = _cuda(hm).requires_grad_(True)
@@ -218,9 +224,12 @@ def test_resident_launch_writes_the_loss_scalar_itself():
     ref_loss = O.joint_location_loss(hm.astype(np.float64), gt, vis)
     assert abs(vals[0] - ref_loss) <= 1e-5 * abs(ref_loss)
     ops.KERNEL_EVENTS = {}
+    saved = ops.FUSED_MODE
+    ops.FUSED_MODE = "resident"
     try:
         xg = _cuda(hm).requires_grad_(True)
-        L.JointLocationLoss()(xg, _cuda(gt), _cuda(vis)).backward()
+        L.JointLocationLoss(fused=True)(xg, _cuda(gt), _cuda(vis)).backward()
         assert "joint_loss_resident" in ops.KERNEL_EVENTS and "sum_f64" not in ops.KERNEL_EVENTS
     finally:
         ops.KERNEL_EVENTS = None
+        ops.FUSED_MODE = saved
