@@ -763,12 +763,12 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
         };
         auto compute = [&](const uint4 (&raw)[kKP]) {
             if (active) {
-                const float rowB = kz * ((zbf - Ezh) - Ezl);
+                const float dzs = (zbf - Ezh) - Ezl;             // z_stage - Ez, absolute accuracy kept
 #pragma unroll
                 for (int q = 0; q < kKP; ++q) {
                     float rtv;
                     if (hoist) {
-                        rtv = rowA[q] + rowB;
+                        rtv = fmaf(kz, dzs, rowA[q]);
                     } else {
                         const float y = ybf + yof[q], z = zbf + zof[q];
                         rtv = fmaf(ky, (y - Eyh) - Eyl, kz * ((z - Ezh) - Ezl));

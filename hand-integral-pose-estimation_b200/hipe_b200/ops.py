@@ -219,8 +219,8 @@ def _fused_plan(logits, n_vol, D, H, W):
       "cluster"  the cluster-resident launch (hipe_joint_loss_cluster: every volume held in the
                  distributed shared memory of one thread-block cluster, one HBM read + one write,
                  nothing in L2) for the geometries its loops are specialised for -- 4096- or
-                 3136-byte visits with every stage starting at y = 0, i.e. 64^3, 32^3 and 56^3 in
-                 fp32 and bf16: fp32 64^3 x 1344 0.495 ms vs 0.540 resident / 0.565 stream, x 672 0.265
+                 3136-byte visits with every stage starting at y = 0, i.e. 64^3 and 32^3 in fp32 and
+                 bf16, 56^3 in fp32 (x 672: 0.177 ms vs 0.202 stream; x 2016: 0.530 vs 0.576): fp32 64^3 x 1344 0.495 ms vs 0.540 resident / 0.565 stream, x 672 0.265
                  vs 0.301; bf16 64^3 x 10752 2.37 vs 2.61 stream, x 1344 0.317 vs 0.332; fp32 32^3 x
                  5376 0.25 vs 0.278;
       "stream"   one launch whose second read goes through L2 (hipe_joint_loss_fused) for every other
@@ -239,7 +239,9 @@ def _fused_plan(logits, n_vol, D, H, W):
         if cp is not None:
             stage_bytes, row_bytes = cp[3], W * esz
             sr = stage_bytes // row_bytes                       # rows per stage
-            if stage_bytes in (16384, 12544) and sr % H == 0:   # the specialised loops
+            # the specialised loops; 2-byte 56^3 (12.25 KB stages on 2 CTAs) is the one case among them
+            # where the stream launch is still ahead (bf16 56^3 x 2016: 0.328 ms vs 0.366)
+            if sr % H == 0 and (stage_bytes == 16384 or (stage_bytes == 12544 and esz == 4)):
                 return "cluster"
     if (W * esz) % 16 == 0 and vol_bytes >= (1 << 17):
         return "stream"

@@ -93,6 +93,8 @@ def test_many_volumes_per_cluster_and_reproducible(monkeypatch):
     out2 = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
     assert torch.equal(out[4], out2[4]) and torch.equal(out[0], out2[0]) and torch.equal(out[3], out2[3])
     # a small ring (3 slots of look-ahead only) and a tiny grid (one cluster walks everything)
+    # and the plain-store exchange; the general (non-specialised) loops are another compilation of the
+    # same arithmetic: held to the oracle, not to the bits
     for env in ({"HIPE_CLUSTER_SLOTS": "9"}, {"HIPE_CLUSTER_GRID": "1"}, {"HIPE_CLUSTER_GRID": "3"},
                 {"HIPE_CLUSTER_STASYNC": "0"}, {"HIPE_CLUSTER_GENERIC": "1"}):
         os.environ.update(env)
@@ -102,7 +104,11 @@ def test_many_volumes_per_cluster_and_reproducible(monkeypatch):
         finally:
             for k_ in env:
                 del os.environ[k_]
-        assert torch.equal(out[4], out3[4]) and torch.equal(out[0], out3[0])
+        if "HIPE_CLUSTER_GENERIC" in env:
+            _check(hm, gt, vis, D, H, W, B, J, out3)
+        else:
+            assert torch.equal(out[0], out3[0]) and torch.equal(out[3], out3[3]), env
+            assert torch.equal(out[4], out3[4]), (env, (out[4] - out3[4]).abs().max().item())
 
 
 def test_cluster_agrees_with_two_launch_path():
