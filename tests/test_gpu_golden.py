@@ -9,6 +9,8 @@ import numpy as np
 import pytest
 import torch
 
+from oracle import integral_np as O
+from tests import synth
 from tests.test_oracle_golden import J, SMALL, case_input, gold
 
 pytestmark = pytest.mark.gpu
