@@ -204,7 +204,11 @@ class _PeerExchange:
         # split form: one word per rank in pinned host memory the collect kernel writes straight into
         # (UVA), so the host can see a timeout -- and WHICH rank is missing -- without synchronising
         self.err_host = torch.zeros(world, dtype=torch.int32).pin_memory()
+        self.err_np = self.err_host.numpy()          # host view: reading it costs no torch dispatch
+        self.err_ptr = self.err_host.data_ptr()
+        self._lib = lib
         self.scratch = torch.zeros(world + 1, dtype=torch.float64, device=device)
+        self.scratch_ptr = self.scratch.data_ptr()
         self.value = torch.empty(2, dtype=torch.float64, device=device)      # alternating outputs
         self.coords_all = [torch.empty((world * b, k), dtype=torch.float64, device=device) for _ in range(2)]
         self.seq = 0
@@ -239,47 +243,59 @@ class _PeerExchange:
         """-> (value 0-dim `out_dtype`, coords_all (world*b, k) fp64, event).  The two tensors are
         written on the side stream; `event` fires when they are complete."""
         from . import _lib, ops
-        lib = _lib.load()
+        lib = self._lib
         dev = coords.device
-        self.check()
+        if self.err_np.any():
+            self.check()
         main = torch.cuda.current_stream(dev)
         # flow control (see hipe_exchange.cu): publish(t) only after this rank's collect(t-1)
-        self._join_side(dev)
+        if self.last_col is not None:
+            main.wait_event(self.last_col)
         self.seq += 1
         i = self.seq & 3
+        ev_pub, ev_col, side = self.ev_pub[i], self.ev_col[i], self.side
         with ops._launch("peer_publish", coords):
             _lib.check(lib.hipe_peer_publish(
                 loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
                 self.peers_dev, self.world, self.rank, self.seq, main.cuda_stream))
-        self.ev_pub[i].record(main)
+        ev_pub.record(main)
         value = torch.empty((), dtype=torch.float64, device=dev)
         call = torch.empty((self.world * self.b, self.k), dtype=torch.float64, device=dev)
-        with torch.cuda.stream(self.side):
-            self.side.wait_event(self.ev_pub[i])
-            with ops._launch("peer_collect", coords):
-                _lib.check(lib.hipe_peer_collect(
-                    self.peers_dev, self.world, self.rank, self.seq, self.b, self.k, float(value_scale),
-                    value.data_ptr(), None, call.data_ptr(), self.err_host.data_ptr(), self.scratch.data_ptr(),
-                    self.timeout_s, self.side.cuda_stream))
-            out = value if out_dtype == torch.float64 else value.to(out_dtype)
-            self.ev_col[i].record(self.side)
-        for t in (value, call, out):
-            t.record_stream(self.side)
-        self.last_col = self.ev_col[i]
-        return out, call, self.ev_col[i]
+        side.wait_event(ev_pub)
+        ops.LAUNCHES += 1
+        timed = ops.KERNEL_EVENTS is not None
+        if timed:
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record(side)
+        _lib.check(lib.hipe_peer_collect(
+            self.peers_dev, self.world, self.rank, self.seq, self.b, self.k, float(value_scale),
+            value.data_ptr(), None, call.data_ptr(), self.err_ptr, self.scratch_ptr, self.timeout_s, side.cuda_stream))
+        if timed:
+            t1.record(side)
+            ops.KERNEL_EVENTS.setdefault("peer_collect", []).append((t0, t1))
+        out = value
+        if out_dtype != torch.float64:
+            with torch.cuda.stream(side):
+                out = value.to(out_dtype)
+            out.record_stream(side)
+        ev_col.record(side)
+        value.record_stream(side)
+        call.record_stream(side)
+        self.last_col = ev_col
+        return out, call, ev_col
 
     def check(self):
         """Raise if an earlier collect gave up waiting (no synchronisation: the kernel writes the
         words into pinned host memory)."""
-        if bool(self.err_host.any()):
-            missing = [r for r in range(self.world) if int(self.err_host[r]) != 0]
+        if self.err_np.any():
+            missing = [r for r in range(self.world) if int(self.err_np[r]) != 0]
             raise RuntimeError("hipe_b200 peer exchange: rank(s) %s did not publish their record within %.0f s "
                                "(a rank skipped a step, crashed or is stalled); the global loss of that step is NaN"
                                % (missing, self.timeout_s))
 
     def timed_out(self):
         torch.cuda.synchronize(self.buf.device)
-        return bool(self.err.item() != 0) or bool(self.err_host.any())
+        return bool(self.err.item() != 0) or bool(self.err_np.any())
 
 
 def _peer_exchange_wanted(group, device):

@@ -8,7 +8,9 @@ out = os.path.join(ROOT, "profiles")
 os.makedirs(out, exist_ok=True)
 
 # ---- launch list (gpu__time_duration.sum per launch; cold-cache, serialised: compare SHARES) ----
-lp = os.path.join(ROOT, "gpurun_out", "launches.csv")
+lp = os.path.join(ROOT, "gpurun_out", "%s_launches.csv" % tag)
+if not os.path.exists(lp):
+    lp = os.path.join(ROOT, "gpurun_out", "launches.csv")
 if os.path.exists(lp):
     rows = [r for r in csv.reader(open(lp)) if len(r) > 10]
     hdr = rows[0]
@@ -43,11 +45,22 @@ traffic_path = os.path.join(out, "traffic.json")
 traffic = json.load(open(traffic_path)) if os.path.exists(traffic_path) else {}
 md = ["# ncu --set full captures (%s), one launch each, B200, `--clock-control none`\n" % tag]
 BF16_B = os.environ.get("HIPE_NCU_BF16_B", "64")     # batch the bf16 forward capture was taken at
-for name, key, cfgkey in [("%s_resident_f32" % tag, "resident", "f32_64_B64"),
-                          ("%s_fwd_f32" % tag, "softargmax_fwd", "f32_64_B64"),
-                          ("%s_fwd_bf16" % tag, "softargmax_fwd", "bf16_64_B%s" % BF16_B),
-                          ("%s_bwd_f32" % tag, "softargmax_bwd", "f32_64_B64"), ("%s_fused_f32" % tag, "fused", "f32_64_B64"),
-                          ("%s_fused_bf16" % tag, "fused", "bf16_64_B128")]:
+try:
+    COMMIT = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+except Exception:
+    COMMIT = None
+CAPTURES = [("%s_resident_f32" % tag, "resident", "f32_64_B64"),
+            ("%s_fwd_f32" % tag, "softargmax_fwd", "f32_64_B64"),
+            ("%s_fwd_bf16" % tag, "softargmax_fwd", "bf16_64_B%s" % BF16_B),
+            ("%s_bwd_f32" % tag, "softargmax_bwd", "f32_64_B64"), ("%s_fused_f32" % tag, "fused", "f32_64_B64"),
+            ("%s_fused_bf16" % tag, "fused", "bf16_64_B128"),
+            # round 2: <tag>_<kernel>_<dtype>_<dim>_B<batch>
+            ("%s_cluster_f32_64_B64" % tag, "cluster", "f32_64_B64"),
+            ("%s_cluster_bf16_64_B512" % tag, "cluster", "bf16_64_B512"),
+            ("%s_cluster_f32_56_B32" % tag, "cluster", "f32_56_B32"),
+            ("%s_fused_f32_96_B32" % tag, "fused", "f32_96_B32"),
+            ("%s_fwd_f32_64_B32" % tag, "softargmax_fwd", "f32_64_B32")]
+for name, key, cfgkey in CAPTURES:
     rep = os.path.join(ROOT, "gpurun_out", name + ".ncu-rep")
     if not os.path.exists(rep):
         continue
@@ -64,7 +77,7 @@ for name, key, cfgkey in [("%s_resident_f32" % tag, "resident", "f32_64_B64"),
         return float(v.replace(",", "")) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
     tr = to_bytes(d["dram__bytes_read.sum"]) + to_bytes(d["dram__bytes_write.sum"])
     md.append("| **dram read + write per launch** | %.4f GB |" % (tr / 1e9))
-    traffic.setdefault(key, {})[cfgkey] = tr
+    traffic.setdefault(key, {})[cfgkey] = {"bytes": tr, "capture": name, "commit": COMMIT}
     # hottest SASS by stall samples
     src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     srows = list(csv.reader(src.splitlines()))
