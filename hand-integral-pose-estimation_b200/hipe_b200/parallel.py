@@ -204,6 +204,8 @@ class _PeerExchange:
         # split form: one word per rank in pinned host memory the collect kernel writes straight into
         # (UVA), so the host can see a timeout -- and WHICH rank is missing -- without synchronising
         self.err_host = torch.zeros(world, dtype=torch.int32).pin_memory()
+        self.call_ring = [torch.empty((world * b, k), dtype=torch.float64, device=device) for _ in range(4)]
+        self.keep = [None] * 4
         self.err_np = self.err_host.numpy()          # host view: reading it costs no torch dispatch
         self.err_ptr = self.err_host.data_ptr()
         self._lib = lib
@@ -239,9 +241,11 @@ class _PeerExchange:
             torch.cuda.current_stream(device).wait_event(self.last_col)
             self.last_col = None
 
-    def run_deferred(self, loss_scalar, in_scale, coords, value_scale, out_dtype=torch.float64):
+    def run_deferred(self, loss_scalar, in_scale, coords, value_scale, out_dtype=torch.float64, into=None):
         """-> (value 0-dim `out_dtype`, coords_all (world*b, k) fp64, event).  The two tensors are
-        written on the side stream; `event` fires when they are complete."""
+        written on the side stream; `event` fires when they are complete.  `into`: a 0-dim fp64 tensor
+        that receives the value (the unwritten loss scalar of the single-launch autograd function),
+        else a fresh one.  coords_all is one of four ring buffers: valid until four steps later."""
         from . import _lib, ops
         lib = self._lib
         dev = coords.device
@@ -259,8 +263,11 @@ class _PeerExchange:
                 loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
                 self.peers_dev, self.world, self.rank, self.seq, main.cuda_stream))
         ev_pub.record(main)
-        value = torch.empty((), dtype=torch.float64, device=dev)
-        call = torch.empty((self.world * self.b, self.k), dtype=torch.float64, device=dev)
+        value = into.detach() if into is not None else torch.empty((), dtype=torch.float64, device=dev)
+        call = self.call_ring[i]
+        # the value's storage must outlive the side-stream write even if the caller drops the loss at
+        # once: at most two collects are outstanding (flow control above), four are kept
+        self.keep[i] = value
         side.wait_event(ev_pub)
         ops.LAUNCHES += 1
         timed = ops.KERNEL_EVENTS is not None
@@ -279,8 +286,6 @@ class _PeerExchange:
                 out = value.to(out_dtype)
             out.record_stream(side)
         ev_col.record(side)
-        value.record_stream(side)
-        call.record_stream(side)
         self.last_col = ev_col
         return out, call, ev_col
 
@@ -366,6 +371,8 @@ class ShardedJointLocationLoss(nn.Module):
         self._coords = None
         self._coords64 = None
         self._coords_event = None
+        self._counts_key = None
+        self._counts = None
         self._xch = None
         self._peers = {}             # (world, b, k) -> _PeerExchange: train / val / last short batch each keep theirs
         self._peer_off = False       # True = unavailable on this box (NCCL is used)
@@ -423,7 +430,11 @@ class ShardedJointLocationLoss(nn.Module):
         scaled = terms = None
         px = None
         if self.global_batch is not None:
-            counts = [hi - lo for lo, hi in (shard_bounds(self.global_batch, world, r) for r in range(world))]
+            ck = (self.global_batch, world)
+            if self._counts_key != ck:
+                self._counts = [hi - lo for lo, hi in (shard_bounds(self.global_batch, world, r) for r in range(world))]
+                self._counts_key = ck
+            counts = self._counts
             b_local = heatmap_out.shape[0]
             if counts[dist.get_rank(self.group)] != b_local:
                 raise ValueError("this rank holds %d rows, shard_bounds(%d, %d) gives it %d"
@@ -456,6 +467,7 @@ class ShardedJointLocationLoss(nn.Module):
             if px is None and coords.is_cuda and coords.dtype == torch.float32 and self.local_fn is _local_cuda_loss:
                 px = self._peer_exchange(world, b_local, k, coords.device)
             event = None
+            direct = False
             with torch.no_grad():
                 if px is not None:
                     # NVLink peer memory: (sum the loss terms,) store to all peers, flag; wait, combine
@@ -464,8 +476,12 @@ class ShardedJointLocationLoss(nn.Module):
                         src = src.to(torch.float64)
                     carrier_dtype = scaled.dtype if scaled is not None else loss_sum.dtype
                     if self.defer:
+                        # the collect writes the global value straight into the (so far unwritten) scalar
+                        # the single-launch function returned: no second autograd node around it
+                        into = scaled if (scaled is not None and scaled.dtype == torch.float64) else None
                         value, allc, event = px.run_deferred(src.reshape(-1), 1.0, coords.detach().contiguous(),
-                                                             1.0 / denom, carrier_dtype)
+                                                             1.0 / denom, carrier_dtype, into=into)
+                        direct = into is not None
                     else:
                         value, allc = px.run(src.reshape(-1), 1.0, coords.detach().contiguous(), 1.0 / denom)
                     self.exchange = "peer"
@@ -481,6 +497,10 @@ class ShardedJointLocationLoss(nn.Module):
                     self.exchange = "nccl"
             self._coords, self._coords64 = None, (allc.reshape(world, b_local, k), coords.dtype)
             self._coords_event = event
+            if direct:
+                out = scaled.as_subclass(DeferredLoss)       # outside no_grad: stays attached to the graph
+                out._hipe_event = event
+                return out
             if scaled is not None:
                 carrier = scaled
             else:
