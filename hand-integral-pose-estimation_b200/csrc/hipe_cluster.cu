@@ -84,6 +84,7 @@ struct Params {
     int st_hint;      // gradient stores carry an L2 evict_first hint
     int stasync;      // partial exchange by st.async + transaction bytes (1) or plain stores + remote arrives (0)
     double inv_W, inv_H, inv_D;
+    int sym;          // both teams reduce AND write, alternating volumes (0: team 0 reduces, team 1 writes)
     int hoist;        // H | SR: every stage starts at row y = 0 (row term = per-volume part + per-stage part)
     int poly;         // 2-byte logits: gradient-pass exponentials on the FMA pipe: 0 none, 1 every other visit, 2 all
     // outputs (nullable except out)
@@ -271,6 +272,11 @@ struct Ring {
         off += (uint32_t)slot_bytes;
         if (++slot == nslots) { slot = 0; off = 0; ++lap; }
     }
+    __device__ __forceinline__ void advance(int n, int nslots, int slot_bytes) {
+        slot += n;
+        while (slot >= nslots) { slot -= nslots; ++lap; }
+        off = (uint32_t)slot * (uint32_t)slot_bytes;
+    }
 };
 
 // fp32 >= 0 (normal or zero) -> fp64 without the conversion unit (F2F.F64.F32 shares the quarter-rate
@@ -315,7 +321,7 @@ __device__ __forceinline__ double warp_sum8(const double (&v)[8], int lane) {
 // become immediates and the row bookkeeping collapses.  The launch is instruction-bound (one CTA per
 // SM, every role a dependency chain), so the instructions per stage are what is tuned.  kPass == 0
 // takes any geometry pick_geom accepts.
-template <typename T, int kPass>
+template <typename T, int kPass, bool kSym>
 __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
     using V16 = Vec16<T>;
     constexpr int VEC = V16::N;
@@ -511,12 +517,11 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
     const int zb0 = rowbase0 / p.H, yb0 = rowbase0 - zb0 * p.H;
     const uint32_t lds_base = ring + 16u * tid;
 
-    if (!is_writer) {
-        // =============================== REDUCE team ===============================
-        Ring r;
-        r.init();
-        const double dzd = (double)(p.SR / p.H);      // hoist: z advance per stage
-        for (long long k = 0; k < nv; ++k) {
+    // =============================== reduction of one volume ===============================
+    // (the team's share of volume k: the stages at ring position r, which is advanced past them)
+    auto reduce_volume = [&](long long k, Ring& r) {
+        {
+            const double dzd = (double)(p.SR / p.H);      // hoist: z advance per stage
             const unsigned sb = (unsigned)(k % kPB);
             float m = kNegInf, mL = kNegInf, tm = kNegInf;   // offset in use, fl(m*log2e), true maximum
             float2 c2[kKP][VEC / 2];
@@ -672,26 +677,22 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
             if (lane == 0) mbar_arrive(smem_u32(&sm.red_ready[sb]));
             if (warp == 0) CLU_TRACE(k, 3);
         }
-        CLU_TOTAL(9, 1, 2, -1);
-        return;
-    }
+    };
 
-    // ================================ WRITE team ================================
-    // row offsets of this thread's kKP visits inside a stage, as exact small floats
-    float yof[kKP], zof[kKP];
+    // ============================== gradient write of one volume ==============================
+    auto write_volume = [&](long long k, Ring& r) {
+        // row offsets of this thread's kKP visits inside a stage, as exact small floats
+        float yof[kKP], zof[kKP];
 #pragma unroll
-    for (int q = 0; q < kKP; ++q) {
-        const int rho = rr + q * p.R;
-        const int zo = rho / p.H;
-        zof[q] = (float)zo;
-        yof[q] = (float)(rho - zo * p.H);
-    }
-    const float Hf = (float)p.H, SRf = (float)p.SR, dzf = (float)(p.SR / p.H);
-    const uint64_t st_pol = policy_evict_first();
-    const float2 l2e2 = make_float2(kLog2e, kLog2e);
-    Ring r;
-    r.init();
-    for (long long k = 0; k < nv; ++k) {
+        for (int q = 0; q < kKP; ++q) {
+            const int rho = rr + q * p.R;
+            const int zo = rho / p.H;
+            zof[q] = (float)zo;
+            yof[q] = (float)(rho - zo * p.H);
+        }
+        const float Hf = (float)p.H, SRf = (float)p.SR, dzf = (float)(p.SR / p.H);
+        const uint64_t st_pol = policy_evict_first();
+        const float2 l2e2 = make_float2(kLog2e, kLog2e);
         const long long vol = cluster_id + k * p.n_clusters;
         const unsigned rb = (unsigned)(k % kNB);
         CLU_WAIT(6, wait_cta(smem_u32(&sm.scal_ready[rb]), (uint32_t)(k / kNB) & 1));
@@ -811,17 +812,47 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
             }
         }
         if (warp == 0) CLU_TRACE(k, 9);
+    };
+
+    // Team roles.  Specialised (default): team 0 reduces every volume, team 1 writes every volume.
+    // Symmetric (HIPE_CLUSTER_SYM=1, an experiment): each team takes every other volume and does both
+    // passes on it, so that two gradient writes could overlap for 2-byte logits, whose gradient pass
+    // is the bottleneck.  Measured slower on every shape (bf16 64^3 x 2688: 0.641 vs 0.562 ms; fp32
+    // 64^3: 0.631 vs 0.487): a team now idles through its own volume's merge, and the ring never holds
+    // enough of the next volume for two writes to overlap much.
+    if constexpr (!kSym) {
+        Ring r;
+        r.init();
+        if (!is_writer) {
+            for (long long k = 0; k < nv; ++k) reduce_volume(k, r);
+            CLU_TOTAL(9, 1, 2, -1);
+            return;
+        }
+        for (long long k = 0; k < nv; ++k) write_volume(k, r);
+    } else {
+        const int team = is_writer ? 1 : 0;
+        Ring r;
+        r.init();
+        for (long long k = 0; k < nv; ++k) {
+            if ((int)(k & 1) == team) {
+                Ring rw = r;
+                reduce_volume(k, r);
+                write_volume(k, rw);
+            } else {
+                r.advance(nst, p.nslots, slot_bytes);
+            }
+        }
     }
-    // The loss scalar without a second launch: rank 0's first write warps are the writers of
-    // loss_terms, so the last of them to finish sums the terms (fixed order: lane-strided partials,
-    // then the shuffle tree) -- loss.py:88-89.
+    // The loss scalar without a second launch: rank 0's first warps of the writing teams are the
+    // writers of loss_terms, so the last of them to finish sums the terms (fixed order: lane-strided
+    // partials, then the shuffle tree) -- loss.py:88-89.
     if (crank == 0 && warp == 0 && p.loss_out && p.loss_terms) {
         __threadfence();
         __syncwarp();
         unsigned t = 0;
         if (lane == 0) t = atomicAdd(p.ticket, 1u);
         t = __shfl_sync(0xffffffffu, t, 0);
-        if (t == (unsigned)p.n_clusters - 1) {
+        if (t == (unsigned)p.n_clusters * (kSym ? 2u : 1u) - 1u) {
             __threadfence();
             double acc = 0.0;
             for (long long i = lane; i < p.n_vol * 3; i += 32) acc += __ldcg(p.loss_terms + i);
@@ -872,21 +903,24 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
     // Cluster size.  What a B200 can hold at once (cudaOccupancyMaxActiveClusters with this kernel's
     // footprint, profiles/r2_cluster_occupancy.md): clusters of 1 / 2 CTAs reach all 148 SMs, 3 -> 135,
     // 4 -> 132, 5 -> 130, 6 -> 132, 7 -> 105, 8 -> 120.  Among the sizes whose largest share leaves
-    // kMinSpare slots of look-ahead, take the one that keeps the most SMs busy (ties: the larger
-    // cluster, i.e. the smaller share).  Measured on 64^3: fp32 C=6 0.505 ms vs C=8 0.518, C=5 0.550,
-    // C=7 0.622; bf16 C=3 0.638 vs C=4 0.652, C=5 0.738.
+    // kMinSpare slots of look-ahead, take the best score = SMs in use, less 1 % per slot of look-ahead
+    // short of 6 (ties: the smaller cluster -- fewer partials to wait for).  Measured on 64^3 (ms, 1344 fp32 /
+    // 2688 bf16 volumes): fp32 C=6 0.487 vs C=8 0.518, C=5 0.511, C=7 0.59; bf16 C=4 0.562 vs C=3
+    // 0.588, C=5 0.66; fp32 56^3 x 672: C=6 0.177 vs C=8 0.183, C=5 0.185, C=4 0.187.
     static const int kSMs[kMaxCluster + 1] = {0, 148, 148, 135, 132, 130, 132, 105, 120};
     int want = 0;
     if (const char* env = getenv("HIPE_CLUSTER_C")) want = atoi(env);
     g->C = 0;
-    int best = -1;
+    double best = -1.0;
     for (int C = 1; C <= kMaxCluster; ++C) {
         if (want && C != want) continue;
         if (g->NSv < C) break;
         const int share = (g->NSv + C - 1) / C;
         if (share + (want ? 1 : kMinSpare) > nslots) continue;
-        if (kSMs[C] >= best) {
-            best = kSMs[C];
+        const int spare = nslots - share;
+        const double score = kSMs[C] * (1.0 - 0.01 * (spare < 6 ? 6 - spare : 0));
+        if (score > best) {
+            best = score;
             g->C = C;
             g->max_share = share;
         }
@@ -895,9 +929,9 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
     return g->C > 0;
 }
 
-template <typename T, int kPass>
+template <typename T, int kPass, bool kSym>
 static int launch(const Params& p0, const Geom& g, cudaStream_t st) {
-    auto kern = k_cluster<T, kPass>;
+    auto kern = k_cluster<T, kPass, kSym>;
     const size_t smem = (size_t)g.nslots * g.slot_bytes + sizeof(Smem);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -1022,15 +1056,18 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     if (e != cudaSuccess) return (int)e;
     p.hoist = (g.SR % H == 0) ? 1 : 0;
     p.inv_W = 1.0 / (double)W; p.inv_H = 1.0 / (double)H; p.inv_D = 1.0 / (double)D;
+    p.sym = 0;     // symmetric teams: an experiment that lost on every shape (profiles/r2_configs.md)
+    if (const char* env = getenv("HIPE_CLUSTER_SYM")) p.sym = (env[0] != '0') ? 1 : 0;
     p.stasync = 1;
     if (const char* env = getenv("HIPE_CLUSTER_STASYNC")) p.stasync = (env[0] != '0') ? 1 : 0;
     int pass = 0;      // specialised geometry?
     if (p.hoist && g.stage_bytes == 4 * g.pass_bytes && g.slot_bytes == g.stage_bytes && g.nact * 16 == g.pass_bytes &&
         !getenv("HIPE_CLUSTER_GENERIC"))
         pass = (g.pass_bytes == 4096 || g.pass_bytes == 3136) ? g.pass_bytes : 0;
-    if (dtype == HIPE_F32)
-        return pass == 4096 ? clu::launch<float, 4096>(p, g, st)
-                            : (pass == 3136 ? clu::launch<float, 3136>(p, g, st) : clu::launch<float, 0>(p, g, st));
-    return pass == 4096 ? clu::launch<__nv_bfloat16, 4096>(p, g, st)
-                        : (pass == 3136 ? clu::launch<__nv_bfloat16, 3136>(p, g, st) : clu::launch<__nv_bfloat16, 0>(p, g, st));
+#define HIPE_CLU_LAUNCH(T, SYM)                                                                   \
+    (pass == 4096 ? clu::launch<T, 4096, SYM>(p, g, st)                                          \
+                  : (pass == 3136 ? clu::launch<T, 3136, SYM>(p, g, st) : clu::launch<T, 0, SYM>(p, g, st)))
+    if (dtype == HIPE_F32) return p.sym ? HIPE_CLU_LAUNCH(float, true) : HIPE_CLU_LAUNCH(float, false);
+    return p.sym ? HIPE_CLU_LAUNCH(__nv_bfloat16, true) : HIPE_CLU_LAUNCH(__nv_bfloat16, false);
+#undef HIPE_CLU_LAUNCH
 }

@@ -71,7 +71,7 @@ def case(dt, D, B, envs):
             if plan is None:
                 print("  cluster %s: unsupported" % env)
                 continue
-            rec("cluster %s C=%d slots=%d share=%d" % (",".join("%s=%s" % (k[13:], v) for k, v in env.items()), plan[0], plan[1], plan[2]),
+            rec("cluster %s C=%d share=%d" % (",".join("%s=%s" % (k[13:], v) for k, v in env.items()), plan[0], plan[2]),
                 lambda x: ops.joint_loss_cluster(x, n_vol, D, D, D, gt, vis, 1.0 / B, loss_out=loss))
         finally:
             for k in env:
@@ -93,6 +93,15 @@ if __name__ == "__main__":
         case(f32, 56, 96, [{}, {"HIPE_CLUSTER_GENERIC": "1"}, {"HIPE_CLUSTER_C": "4"}, {"HIPE_CLUSTER_C": "5"}, {"HIPE_CLUSTER_C": "8"}])
         case(bf, 56, 96, [{}, {"HIPE_CLUSTER_C": "3"}, {"HIPE_CLUSTER_C": "4"}])
         case(f32, 64, 64, [{}])
+        sys.exit(0)
+    if "sym" in sys.argv:
+        S1, S0 = {"HIPE_CLUSTER_SYM": "1"}, {"HIPE_CLUSTER_SYM": "0"}
+        case(bf, 64, 128, [S1, S0, dict(S1, HIPE_CLUSTER_C="4"), dict(S0, HIPE_CLUSTER_C="4"), dict(S1, HIPE_CLUSTER_C="5"),
+                           dict(S1, HIPE_CLUSTER_C="6"), dict(S1, HIPE_CLUSTER_C="8"), dict(S1, HIPE_CLUSTER_C="4", HIPE_CLUSTER_POLY="1")])
+        case(bf, 64, 512, [S1, S0, dict(S1, HIPE_CLUSTER_C="4"), dict(S1, HIPE_CLUSTER_C="6")])
+        case(f32, 64, 64, [S0, S1, dict(S1, HIPE_CLUSTER_C="8"), dict(S1, HIPE_CLUSTER_C="7")])
+        case(f32, 56, 32, [S0, S1, dict(S1, HIPE_CLUSTER_C="8")])
+        case(bf, 56, 96, [S1, S0, dict(S1, HIPE_CLUSTER_C="3"), dict(S1, HIPE_CLUSTER_C="4")])
         sys.exit(0)
     case(f32, 64, 64, [{}, {"HIPE_CLUSTER_STASYNC": "0"}, {"HIPE_CLUSTER_C": "8"}, {"HIPE_CLUSTER_C": "5"}])
     case(bf, 64, 128, [{}, {"HIPE_CLUSTER_POLY": "1"}, {"HIPE_CLUSTER_C": "4"}])

@@ -92,7 +92,7 @@ def test_launch_plan_host_logic():
     assert plan(torch.float64, 1344, 64) is None
     # the plan query behind "cluster": cluster size, ring slots, stages per share, bytes per stage
     assert ops.cluster_plan(torch.empty(0), 1344, 64, 64, 64) == (6, 14, 11, 16384)
-    assert ops.cluster_plan(torch.empty(0, dtype=torch.bfloat16), 1344, 64, 64, 64) == (3, 14, 11, 16384)
+    assert ops.cluster_plan(torch.empty(0, dtype=torch.bfloat16), 1344, 64, 64, 64) == (4, 14, 8, 16384)
     assert ops.cluster_plan(torch.empty(0), 672, 56, 56, 56)[3] == 12544
     assert ops.cluster_plan(torch.empty(0), 672, 96, 96, 96) is None
     # the tiling query behind "resident": supported geometries report a workspace size, others 0

@@ -55,8 +55,9 @@ def test_cluster_unsupported_geometries(geom):
         ops.joint_loss_cluster(x, 21, D, H, W, _cuda(gt), _cuda(vis), 1.0)
 
 
+@pytest.mark.parametrize("sym", ["0", "1"])
 @pytest.mark.parametrize("csize", [1, 2, 3, 4, 5, 6, 7, 8])
-def test_every_cluster_size(csize):
+def test_every_cluster_size(csize, sym, monkeypatch):
     """Forced cluster sizes, powers of two or not (uneven shares): 32^3 fp32 has 8 stages."""
     from hipe_b200 import ops
     D = H = W = 32
@@ -64,6 +65,7 @@ def test_every_cluster_size(csize):
     hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=17)
     gt, vis = synth.targets(B, J, seed=17)
     x = _cuda(hm)
+    monkeypatch.setenv("HIPE_CLUSTER_SYM", sym)      # team roles: specialised / symmetric
     os.environ["HIPE_CLUSTER_C"] = str(csize)
     try:
         assert ops.cluster_plan(x, B * J, D, H, W)[0] == csize
@@ -96,7 +98,7 @@ def test_many_volumes_per_cluster_and_reproducible(monkeypatch):
     # and the plain-store exchange; the general (non-specialised) loops are another compilation of the
     # same arithmetic: held to the oracle, not to the bits
     for env in ({"HIPE_CLUSTER_SLOTS": "9"}, {"HIPE_CLUSTER_GRID": "1"}, {"HIPE_CLUSTER_GRID": "3"},
-                {"HIPE_CLUSTER_STASYNC": "0"}, {"HIPE_CLUSTER_GENERIC": "1"}):
+                {"HIPE_CLUSTER_STASYNC": "0"}, {"HIPE_CLUSTER_SYM": "1"}, {"HIPE_CLUSTER_GENERIC": "1"}):
         os.environ.update(env)
         try:
             out3 = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
@@ -104,7 +106,7 @@ def test_many_volumes_per_cluster_and_reproducible(monkeypatch):
         finally:
             for k_ in env:
                 del os.environ[k_]
-        if "HIPE_CLUSTER_GENERIC" in env:
+        if "HIPE_CLUSTER_GENERIC" in env or "HIPE_CLUSTER_SYM" in env:
             _check(hm, gt, vis, D, H, W, B, J, out3)
         else:
             assert torch.equal(out[0], out3[0]) and torch.equal(out[3], out3[3]), env
