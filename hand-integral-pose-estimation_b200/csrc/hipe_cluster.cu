@@ -61,6 +61,9 @@ constexpr int kThreads = 2 * kC + 64; // two teams + producer warp + merge warp
 // must stay <= 16384, i.e. <= 102 registers per thread (112 makes the launch impossible: the
 // occupancy query answers 0 clusters)
 constexpr int kMaxRegs = 96;
+// Two write teams (kMode 2, 2-byte logits): 26 warps = 7 on the fullest partition -> <= 73 registers.
+constexpr int kMaxRegs2 = 72;
+constexpr int kThreads2 = 3 * kC + 64;
 constexpr float kLazy = 16.f;         // lazy re-basing threshold of the online softmax
 constexpr int kSmemMax = 232448;      // 227 KB: the opt-in dynamic shared memory of one CTA
 constexpr int kMinSpare = 3;          // slots beyond one share the ring must have (look-ahead)
@@ -81,12 +84,11 @@ struct Params {
     int nslots;       // ring slots per CTA
     int slot_bytes;   // stage_bytes rounded up to 128
     int n_clusters;
-    int st_hint;      // gradient stores carry an L2 evict_first hint
     int stasync;      // partial exchange by st.async + transaction bytes (1) or plain stores + remote arrives (0)
     double inv_W, inv_H, inv_D;
+    int wteams2;      // two write teams taking alternate stages (832 threads, 72 registers)
     int sym;          // both teams reduce AND write, alternating volumes (0: team 0 reduces, team 1 writes)
     int hoist;        // H | SR: every stage starts at row y = 0 (row term = per-volume part + per-stage part)
-    int poly;         // 2-byte logits: gradient-pass exponentials on the FMA pipe: 0 none, 1 every other visit, 2 all
     // outputs (nullable except out)
     float* coords;
     double* expect;
@@ -129,8 +131,8 @@ struct Smem {
 //   3 merge: red_ready          4 merge: peers' partials        5 merge: scal_free
 //   6 write: scal_ready         7 write: full (already landed)
 //   8 producer total   9 reduce total   10 merge total   11 write total   (warp-cycles)
-constexpr int kProfN = 12;
 #ifdef HIPE_CLU_PROF
+constexpr int kProfN = 12;
 __device__ unsigned long long g_prof[kProfN];
 // per-warp register accumulators (three wait classes per role at most), flushed once at role exit:
 // an atomic per wait would itself become the bottleneck
@@ -241,6 +243,12 @@ __device__ __forceinline__ float rebase_w(float m_from, float m_to) {
     return (m_from == kNegInf) ? 0.f : ex2(__fsub_rn(__fmul_rn(m_from, kLog2e), __fmul_rn(m_to, kLog2e)));
 }
 
+// Build option (-DHIPE_CLU_POLY=1|2, off): evaluate every other / every exponential of the 2-byte gradient
+// pass with ex2_poly2 below.  Measured slower (bf16 64^3 x 2688: 0.618 -> 0.630 / 0.74 ms): the launch is
+// bound by the latency of each warp's chain, not by XU throughput, and the polynomial is a longer chain.
+#ifndef HIPE_CLU_POLY
+#define HIPE_CLU_POLY 0
+#endif
 // 2^a for a <= ~0 on the FMA / ALU pipes instead of the quarter-rate XU (MUFU.EX2): round-to-nearest
 // split a = n + f through the 1.5 * 2^23 constant, a degree-4 minimax polynomial for 2^f on
 // [-0.5, 0.5] (relative error 2.7e-6, far below the bf16 output's 2^-9 rounding) in packed FFMA2,
@@ -321,8 +329,11 @@ __device__ __forceinline__ double warp_sum8(const double (&v)[8], int lane) {
 // become immediates and the row bookkeeping collapses.  The launch is instruction-bound (one CTA per
 // SM, every role a dependency chain), so the instructions per stage are what is tuned.  kPass == 0
 // takes any geometry pick_geom accepts.
-template <typename T, int kPass, bool kSym>
-__global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
+template <typename T, int kPass, int kMode>
+__global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const Params p) {
+    constexpr bool kSym = kMode == 1;
+    constexpr int kWT = kMode == 2 ? 2 : 1;             // write teams
+    constexpr int kTeamThreads = (1 + kWT) * kC;
     using V16 = Vec16<T>;
     constexpr int VEC = V16::N;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -355,7 +366,7 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
 #pragma unroll
         for (int s = 0; s < kNB; ++s) {
             mbar_init(smem_u32(&sm.scal_ready[s]), 1);
-            mbar_init(smem_u32(&sm.scal_free[s]), kNW);
+            mbar_init(smem_u32(&sm.scal_free[s]), kNW * kWT);
         }
         // st.async exchange: one local arrive.expect_tx per volume, the peers' stores complete the bytes;
         // plain-store exchange: one remote arrive per peer
@@ -372,7 +383,7 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
     unsigned long long prof_acc_[3] = {0ull, 0ull, 0ull};
 #endif
 
-    if (threadIdx.x >= 2 * kC + 32) {
+    if (threadIdx.x >= kTeamThreads + 32) {
         // ------------------------------- merge warp -------------------------------
         // Lane l (< 7) owns sum number l through both merges, lane 7 the maximum: every merge is a short
         // sequential sum in a fixed order per lane (no shuffle trees on this warp's critical path).
@@ -481,7 +492,7 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
         return;
     }
 
-    if (threadIdx.x >= 2 * kC) {
+    if (threadIdx.x >= kTeamThreads) {
         // ------------------------------- producer warp -------------------------------
         if ((threadIdx.x & 31) == 0) {
             const uint64_t pol = policy_evict_first();
@@ -507,7 +518,8 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
     }
 
     const bool is_writer = threadIdx.x >= kC;
-    const int tid = is_writer ? threadIdx.x - kC : threadIdx.x;   // team-local
+    const int wt = is_writer ? (int)(threadIdx.x / kC) - 1 : 0;   // which write team (kMode 2: 0 or 1)
+    const int tid = threadIdx.x % kC;                             // team-local
     const int lane = tid & 31, warp = tid >> 5;
     const bool active = kFix ? (kPass / 16 >= kC || tid < kPass / 16) : (tid < p.nact);
     const int cg = active ? tid % p.G : 0;
@@ -691,7 +703,6 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
             yof[q] = (float)(rho - zo * p.H);
         }
         const float Hf = (float)p.H, SRf = (float)p.SR, dzf = (float)(p.SR / p.H);
-        const uint64_t st_pol = policy_evict_first();
         const float2 l2e2 = make_float2(kLog2e, kLog2e);
         const long long vol = cluster_id + k * p.n_clusters;
         const unsigned rb = (unsigned)(k % kNB);
@@ -702,7 +713,7 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
         const float ky = (float)rec.K[1], kz = (float)rec.K[2];
         const float ML = __fmul_rn(rec.M, kLog2e);
         uint32_t dep_out = 0;
-        if (crank == 0 && warp == 0) {
+        if (crank == 0 && warp == 0 && wt == 0) {
             // the volume's outputs (rank 0's first write warp: lanes 0-2 one axis each)
             if (lane < 3) {
                 const double term = rec.term[lane], ea = rec.E[lane];
@@ -782,15 +793,16 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
                         const float2 a2 = __ffma2_rn(make_float2(v[2 * j], v[2 * j + 1]), l2e2, nML2);
                         const float2 w2 = __fadd2_rn(ax2[j], rt2);
                         float2 e2;
-                        if (VEC == 8 && (p.poly == 2 || (p.poly == 1 && (q & 1)))) e2 = ex2_poly2(a2);
-                        else e2 = make_float2(ex2(a2.x), ex2(a2.y));
+#if HIPE_CLU_POLY
+                        if (VEC == 8 && (HIPE_CLU_POLY == 2 || (q & 1))) e2 = ex2_poly2(a2);
+                        else
+#endif
+                        e2 = make_float2(ex2(a2.x), ex2(a2.y));
                         const float2 o2 = __fmul2_rn(e2, w2);
                         o[2 * j] = o2.x;
                         o[2 * j + 1] = o2.y;
                     }
-                    unsigned char* dst = gdst + q * pass_bytes;
-                    if (p.st_hint) stg_stream_hint(dst, V16::pack(o), st_pol);
-                    else stg_stream(dst, V16::pack(o));
+                    stg_stream(gdst + q * pass_bytes, V16::pack(o));
                 }
             }
             gdst += stage_bytes;
@@ -801,25 +813,50 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
                 while (ybf >= Hf) { ybf -= Hf; zbf += 1.f; }
             }
         };
-        uint4 rawA[kKP], rawB[kKP];
-        fetch(rawA);
-        for (int s = 0; s < nst; s += 2) {
-            if (s + 1 < nst) fetch(rawB);
-            compute(rawA);
-            if (s + 1 < nst) {
-                if (s + 2 < nst) fetch(rawA);
-                compute(rawB);
+        if constexpr (kWT == 1) {
+            uint4 rawA[kKP], rawB[kKP];
+            fetch(rawA);
+            for (int s = 0; s < nst; s += 2) {
+                if (s + 1 < nst) fetch(rawB);
+                compute(rawA);
+                if (s + 1 < nst) {
+                    if (s + 2 < nst) fetch(rawA);
+                    compute(rawB);
+                }
+            }
+        } else {
+            // two write teams: alternate stages of the same volume (each frees the slots it wrote)
+            uint4 rawA[kKP];
+            for (int s = 0; s < nst; ++s) {
+                if ((s & 1) == wt) {
+                    fetch(rawA);
+                    compute(rawA);
+                } else {
+                    r.next(p.nslots, slot_bytes);
+                    gdst += stage_bytes;
+                    if (hoist) {
+                        zbf += dzf;
+                    } else {
+                        ybf += SRf;
+                        while (ybf >= Hf) { ybf -= Hf; zbf += 1.f; }
+                    }
+                }
             }
         }
         if (warp == 0) CLU_TRACE(k, 9);
     };
 
-    // Team roles.  Specialised (default): team 0 reduces every volume, team 1 writes every volume.
-    // Symmetric (HIPE_CLUSTER_SYM=1, an experiment): each team takes every other volume and does both
-    // passes on it, so that two gradient writes could overlap for 2-byte logits, whose gradient pass
-    // is the bottleneck.  Measured slower on every shape (bf16 64^3 x 2688: 0.641 vs 0.562 ms; fp32
-    // 64^3: 0.631 vs 0.487): a team now idles through its own volume's merge, and the ring never holds
-    // enough of the next volume for two writes to overlap much.
+    // Team roles.  kMode 0 (what ships): team 0 reduces every volume, team 1 writes every volume.
+    // Two other layouts were built to relieve the 2-byte gradient pass (the write team is > 90 % busy
+    // there) and both lost on every shape; they compile only with -DHIPE_CLU_EXPERIMENTS and are
+    // selected by HIPE_CLUSTER_SYM=1 / HIPE_CLUSTER_WT2=1:
+    //   kMode 1, symmetric: each team takes every other volume and does both passes on it, so that two
+    //     gradient writes could overlap.  bf16 64^3 x 2688: 0.641 vs 0.562 ms; fp32 64^3: 0.631 vs 0.487:
+    //     a team idles through its own volume's merge, and the ring never holds enough of the next
+    //     volume for two writes to overlap much.
+    //   kMode 2, one reduce team + two write teams on alternate stages (832 threads, hence 72
+    //     registers): bf16 64^3 x 2688: 0.663 vs 0.530 ms; fp32 64^3: 0.796 vs 0.482: the spills and the
+    //     extra warps on the XU pipe (already 72 % busy for bf16, ncu r2) cost more than they hide.
     if constexpr (!kSym) {
         Ring r;
         r.init();
@@ -846,7 +883,7 @@ __global__ void __maxnreg__(kMaxRegs) k_cluster(const Params p) {
     // The loss scalar without a second launch: rank 0's first warps of the writing teams are the
     // writers of loss_terms, so the last of them to finish sums the terms (fixed order: lane-strided
     // partials, then the shuffle tree) -- loss.py:88-89.
-    if (crank == 0 && warp == 0 && p.loss_out && p.loss_terms) {
+    if (crank == 0 && warp == 0 && wt == 0 && p.loss_out && p.loss_terms) {
         __threadfence();
         __syncwarp();
         unsigned t = 0;
@@ -929,14 +966,15 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
     return g->C > 0;
 }
 
-template <typename T, int kPass, bool kSym>
+template <typename T, int kPass, int kMode>
 static int launch(const Params& p0, const Geom& g, cudaStream_t st) {
-    auto kern = k_cluster<T, kPass, kSym>;
+    auto kern = k_cluster<T, kPass, kMode>;
+    constexpr int kBlock = kMode == 2 ? kThreads2 : kThreads;
     const size_t smem = (size_t)g.nslots * g.slot_bytes + sizeof(Smem);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     cudaLaunchConfig_t cfg = {};
-    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.blockDim = dim3(kBlock, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -952,7 +990,7 @@ static int launch(const Params& p0, const Geom& g, cudaStream_t st) {
     e = cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg);
     if (getenv("HIPE_DEBUG"))
         fprintf(stderr, "hipe_cluster: C=%d smem=%zu threads=%d -> cudaOccupancyMaxActiveClusters: %s, %d clusters\n",
-                g.C, smem, kThreads, cudaGetErrorString(e), ncl);
+                g.C, smem, kBlock, cudaGetErrorString(e), ncl);
     if (e != cudaSuccess) { (void)cudaGetLastError(); return (int)e; }
     if (ncl < 1) return HIPE_E_UNSUPPORTED;
     if (const char* env = getenv("HIPE_CLUSTER_GRID")) {
@@ -1042,10 +1080,6 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     p.W = W; p.H = H; p.D = D;
     p.G = g.G; p.R = g.R; p.SR = g.SR; p.stage_bytes = g.stage_bytes; p.pass_bytes = g.pass_bytes;
     p.nact = g.nact; p.NSv = g.NSv; p.nslots = g.nslots; p.slot_bytes = g.slot_bytes;
-    p.st_hint = 0;
-    if (const char* env = getenv("HIPE_ST_HINT")) p.st_hint = (env[0] != '0') ? 1 : 0;
-    p.poly = 0;
-    if (const char* env = getenv("HIPE_CLUSTER_POLY")) p.poly = (env[0] >= '0' && env[0] <= '2') ? env[0] - '0' : 0;
     p.coords = coords; p.expect = expect; p.stats = stats; p.loss_terms = loss_terms;
     p.gt = gt; p.vis = vis; p.tgt_f64 = (tgt_dtype == HIPE_F64); p.norm = norm;
     p.ticket = static_cast<unsigned*>(workspace);
@@ -1056,6 +1090,8 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     if (e != cudaSuccess) return (int)e;
     p.hoist = (g.SR % H == 0) ? 1 : 0;
     p.inv_W = 1.0 / (double)W; p.inv_H = 1.0 / (double)H; p.inv_D = 1.0 / (double)D;
+    p.wteams2 = 0;
+    if (const char* env = getenv("HIPE_CLUSTER_WT2")) p.wteams2 = (env[0] != '0') ? 1 : 0;
     p.sym = 0;     // symmetric teams: an experiment that lost on every shape (profiles/r2_configs.md)
     if (const char* env = getenv("HIPE_CLUSTER_SYM")) p.sym = (env[0] != '0') ? 1 : 0;
     p.stasync = 1;
@@ -1064,10 +1100,15 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     if (p.hoist && g.stage_bytes == 4 * g.pass_bytes && g.slot_bytes == g.stage_bytes && g.nact * 16 == g.pass_bytes &&
         !getenv("HIPE_CLUSTER_GENERIC"))
         pass = (g.pass_bytes == 4096 || g.pass_bytes == 3136) ? g.pass_bytes : 0;
-#define HIPE_CLU_LAUNCH(T, SYM)                                                                   \
-    (pass == 4096 ? clu::launch<T, 4096, SYM>(p, g, st)                                          \
-                  : (pass == 3136 ? clu::launch<T, 3136, SYM>(p, g, st) : clu::launch<T, 0, SYM>(p, g, st)))
-    if (dtype == HIPE_F32) return p.sym ? HIPE_CLU_LAUNCH(float, true) : HIPE_CLU_LAUNCH(float, false);
-    return p.sym ? HIPE_CLU_LAUNCH(__nv_bfloat16, true) : HIPE_CLU_LAUNCH(__nv_bfloat16, false);
+#define HIPE_CLU_LAUNCH(T, MODE)                                                                   \
+    (pass == 4096 ? clu::launch<T, 4096, MODE>(p, g, st)                                          \
+                  : (pass == 3136 ? clu::launch<T, 3136, MODE>(p, g, st) : clu::launch<T, 0, MODE>(p, g, st)))
+#ifdef HIPE_CLU_EXPERIMENTS
+    // the two team layouts that lost (see the kernel): built only on request
+    const int mode = p.sym ? 1 : p.wteams2 ? 2 : 0;
+    if (mode == 1) return dtype == HIPE_F32 ? HIPE_CLU_LAUNCH(float, 1) : HIPE_CLU_LAUNCH(__nv_bfloat16, 1);
+    if (mode == 2) return dtype == HIPE_F32 ? HIPE_CLU_LAUNCH(float, 2) : HIPE_CLU_LAUNCH(__nv_bfloat16, 2);
+#endif
+    return dtype == HIPE_F32 ? HIPE_CLU_LAUNCH(float, 0) : HIPE_CLU_LAUNCH(__nv_bfloat16, 0);
 #undef HIPE_CLU_LAUNCH
 }

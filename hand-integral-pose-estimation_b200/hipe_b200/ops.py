@@ -220,9 +220,9 @@ def _fused_plan(logits, n_vol, D, H, W):
                  distributed shared memory of one thread-block cluster, one HBM read + one write,
                  nothing in L2) for the geometries its loops are specialised for -- 4096- or
                  3136-byte visits with every stage starting at y = 0, i.e. 64^3 and 32^3 in fp32 and
-                 bf16, 56^3 in fp32 (x 672: 0.177 ms vs 0.202 stream; x 2016: 0.530 vs 0.576): fp32 64^3 x 1344 0.495 ms vs 0.540 resident / 0.565 stream, x 672 0.265
-                 vs 0.301; bf16 64^3 x 10752 2.37 vs 2.61 stream, x 1344 0.317 vs 0.332; fp32 32^3 x
-                 5376 0.25 vs 0.278;
+                 bf16, 56^3 in fp32 (x 672: 0.177 ms vs 0.202 stream; x 2016: 0.530 vs 0.576): fp32 64^3 x 1344 0.482-0.497 ms vs 0.540 resident / 0.556-0.572 stream, x 672
+                 0.265 vs 0.301; bf16 64^3 x 10752 2.09 vs 2.40 stream, x 1344 0.273 vs 0.331; fp32 32^3 x
+                 5376 0.244 vs 0.282; bf16 32^3 (64 KiB volumes) x 5376 0.162 vs 0.224 stream / 0.248 pair;
       "stream"   one launch whose second read goes through L2 (hipe_joint_loss_fused) for every other
                  fp32 / bf16 volume >= 128 KiB (fp32 48^3 x 2016: 0.362 vs 0.42 cluster, 96^3 does not
                  fit a cluster);
@@ -234,7 +234,7 @@ def _fused_plan(logits, n_vol, D, H, W):
     vol_bytes = D * H * W * esz
     if logits.dtype not in (torch.float32, torch.bfloat16):
         return None
-    if vol_bytes >= (1 << 17) and n_vol >= 8:
+    if vol_bytes >= (1 << 16) and n_vol >= 8:
         cp = cluster_plan(logits, n_vol, D, H, W)
         if cp is not None:
             stage_bytes, row_bytes = cp[3], W * esz

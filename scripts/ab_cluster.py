@@ -94,6 +94,15 @@ if __name__ == "__main__":
         case(bf, 56, 96, [{}, {"HIPE_CLUSTER_C": "3"}, {"HIPE_CLUSTER_C": "4"}])
         case(f32, 64, 64, [{}])
         sys.exit(0)
+    if "wt2" in sys.argv:
+        W = {"HIPE_CLUSTER_WT2": "1"}
+        case(bf, 64, 128, [{}, W, dict(W, HIPE_CLUSTER_C="3"), dict(W, HIPE_CLUSTER_C="5"), dict(W, HIPE_CLUSTER_C="6")])
+        case(bf, 64, 512, [{}, W, dict(W, HIPE_CLUSTER_C="3")])
+        case(bf, 64, 64, [{}, W])
+        case(f32, 64, 64, [{}, W, dict(W, HIPE_CLUSTER_C="8")])
+        case(bf, 56, 96, [{}, W, dict(W, HIPE_CLUSTER_C="3")])
+        case(bf, 32, 256, [{}, W])
+        sys.exit(0)
     if "sym" in sys.argv:
         S1, S0 = {"HIPE_CLUSTER_SYM": "1"}, {"HIPE_CLUSTER_SYM": "0"}
         case(bf, 64, 128, [S1, S0, dict(S1, HIPE_CLUSTER_C="4"), dict(S0, HIPE_CLUSTER_C="4"), dict(S1, HIPE_CLUSTER_C="5"),

@@ -88,7 +88,8 @@ def test_launch_plan_host_logic():
     assert plan(torch.float32, 1344, 16) is None            # 16 KB volumes: forward + recompute backward
     assert plan(torch.bfloat16, 2688, 64) == "cluster"
     assert plan(torch.bfloat16, 4032, 56) == "stream"        # the one specialised geometry the stream launch keeps
-    assert plan(torch.bfloat16, 2688, 32) is None
+    assert plan(torch.bfloat16, 2688, 32) == "cluster"     # 64 KB volumes: still ahead of the pair (0.162 vs 0.248 ms)
+    assert plan(torch.bfloat16, 2688, 16) is None
     assert plan(torch.float64, 1344, 64) is None
     # the plan query behind "cluster": cluster size, ring slots, stages per share, bytes per stage
     assert ops.cluster_plan(torch.empty(0), 1344, 64, 64, 64) == (6, 14, 11, 16384)

@@ -197,7 +197,7 @@ def test_bf16_module_default_plan_vs_oracle(geom):
     xb = _cuda(hm32).to(torch.bfloat16)
     up = xb.float().cpu().numpy().astype(np.float64)
     plan = ops.fused_plan(xb, B * J, D, H, W)
-    assert (plan is None) == (D * H * W * 2 < (1 << 17))
+    assert (plan is None) == (D * H * W * 2 < (1 << 16))
     x = xb.clone().requires_grad_(True)
     ops.KERNEL_EVENTS = {}
     try:

@@ -174,7 +174,7 @@ def test_default_module_picks_the_measured_fastest_launch():
     assert ops.fused_plan(x64, 16 * 21, 64, 64, 64) == "cluster"
     assert ops.fused_plan(x64[:2], 42, 64, 64, 64) == "cluster"
     assert ops.fused_plan(x64.bfloat16(), 16 * 21, 64, 64, 64) == "cluster"
-    assert ops.fused_plan(x64.bfloat16()[:, :21 * 32, :32, :32], 16 * 21, 32, 32, 32) is None
+    assert ops.fused_plan(x64.bfloat16()[:, :21 * 32, :32, :32], 16 * 21, 32, 32, 32) == "cluster"
     x56 = torch.empty((2, 21 * 56, 56, 56), device="cuda")
     assert ops.fused_plan(x56, 42, 56, 56, 56) == "cluster"
     x48 = torch.empty((2, 21 * 48, 48, 48), device="cuda")
