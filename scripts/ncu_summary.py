@@ -23,7 +23,9 @@ if os.path.exists(lp):
             pass
     tot = sum(sum(v) for v in agg.values())
     with open(os.path.join(out, "%s_launches.md" % tag), "w") as f:
-        f.write("# ncu launch list of `python bench.py --steps 20 --warmup 3 --no-e2e --no-cpu-baseline` (%s)\n\n" % tag +
+        cmd = ("python bench.py --steps 10 --warmup 3 --blocks 3 --no-e2e --no-cpu-baseline --configs C3,C4" if tag >= "r2"
+               else "python bench.py --steps 20 --warmup 3 --no-e2e --no-cpu-baseline")
+        f.write("# ncu launch list of `%s` (%s)\n\n" % (cmd, tag) +
                 "`ncu --metrics gpu__time_duration.sum --clock-control none -k regex:k_stream|k_l1|...` on one B200; "
                 "per-launch times are cold-cache and serialised, so only the SHARES are comparable with the "
                 "CUDA-event numbers in the bench line.\n\n| kernel | grid | block | launches | mean us | share |\n|---|---|---|---|---|---|\n")
