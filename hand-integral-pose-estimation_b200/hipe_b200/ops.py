@@ -555,7 +555,7 @@ class FusedJointLossFunction(torch.autograd.Function):
     JointLocationLoss(fused=False) for graphs that are back-propagated more than once."""
 
     @staticmethod
-    def forward(ctx, heatmap_out, gt, vis, num_joints, D, H, W, norm, reduce_loss=True):
+    def forward(ctx, heatmap_out, gt, vis, num_joints, D, H, W, norm, reduce_loss=True, loss_cls=None):
         """-> (loss, coords (B, 3J), loss_terms (B*3J,) fp64).  reduce_loss=False leaves the scalar
         unwritten (a carrier for the gradient only): the sharded path sums the terms inside its
         exchange kernel instead of a separate launch."""
@@ -566,6 +566,8 @@ class FusedJointLossFunction(torch.autograd.Function):
         coords, _, _, terms, dlogits = joint_loss_fused(heatmap_out, n_vol, D, H, W, gt, vis, norm,
                                                         loss_out=loss64 if reduce_loss else None, want_aux=False)
         loss = loss64 if out_dtype == torch.float64 else loss64.to(out_dtype)
+        if loss_cls is not None:                 # e.g. parallel.DeferredLoss: the value arrives later, on a side stream
+            loss = loss.as_subclass(loss_cls)
         ctx.dlogits = dlogits                    # not save_for_backward: it is mutated, once, by backward
         ctx.in_shape = heatmap_out.shape
         coords = coords.view(B, num_joints * 3)
@@ -589,7 +591,7 @@ class FusedJointLossFunction(torch.autograd.Function):
             check(_lib.load().hipe_scale_inplace_s(dlogits.data_ptr(), _logits_code(dlogits), dlogits.numel(),
                                                    gs.data_ptr(), _lib.F32 if gs.dtype == torch.float32 else _lib.F64,
                                                    _stream(dlogits)))
-        return dlogits.view(ctx.in_shape), None, None, None, None, None, None, None, None
+        return dlogits.view(ctx.in_shape), None, None, None, None, None, None, None, None, None
 
 
 class Orthonormalize3Function(torch.autograd.Function):

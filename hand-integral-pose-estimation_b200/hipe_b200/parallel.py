@@ -373,6 +373,7 @@ class ShardedJointLocationLoss(nn.Module):
         self._coords_event = None
         self._counts_key = None
         self._counts = None
+        self._fast = {}              # (heatmap shape, dtype) -> cached decisions of the steady-state step
         self._xch = None
         self._peers = {}             # (world, b, k) -> _PeerExchange: train / val / last short batch each keep theirs
         self._peer_off = False       # True = unavailable on this box (NCCL is used)
@@ -424,7 +425,28 @@ class ShardedJointLocationLoss(nn.Module):
     def coords(self, v):
         self._coords, self._coords64, self._coords_event = v, None, None
 
+    def _fast_step(self, fp, heatmap_out, gt_coord, gt_vis):
+        """The steady-state training step (equal shards known a priori, single-launch plan, peer-memory
+        exchange, deferred collect) with the decisions of the first step cached: one autograd node,
+        the loss scalar it returns IS the DeferredLoss the collect fills."""
+        from . import ops
+        px, joint_num, d, h, w, norm, inv_denom, world, b_local, k = fp
+        if gt_coord.dtype != torch.float64:
+            gt_coord = gt_coord.to(torch.float64)
+        if gt_vis.dtype != torch.float64:
+            gt_vis = gt_vis.to(torch.float64)
+        loss, coords, terms = ops.FusedJointLossFunction.apply(heatmap_out, gt_coord, gt_vis, joint_num, d, h, w, norm,
+                                                               False, DeferredLoss)
+        _, allc, event = px.run_deferred(terms, 1.0, coords, inv_denom, torch.float64, into=loss)
+        self._coords, self._coords64, self._coords_event = None, (allc.view(world, b_local, k), coords.dtype), event
+        loss._hipe_event = event
+        return loss
+
     def forward(self, heatmap_out, gt_coord, gt_vis):
+        if self._fast:
+            fp = self._fast.get((heatmap_out.shape, heatmap_out.dtype))
+            if fp is not None and heatmap_out.requires_grad and torch.is_grad_enabled() and heatmap_out.is_contiguous():
+                return self._fast_step(fp, heatmap_out, gt_coord, gt_vis)
         world = dist.get_world_size(self.group)
         counts = None
         scaled = terms = None
@@ -500,6 +522,13 @@ class ShardedJointLocationLoss(nn.Module):
             if direct:
                 out = scaled.as_subclass(DeferredLoss)       # outside no_grad: stays attached to the graph
                 out._hipe_event = event
+                if self.size_average and self.global_batch is not None:
+                    # the next steps of this shape skip every decision taken above
+                    from nets.loss import FreiHandConfig
+                    self._fast[(heatmap_out.shape, heatmap_out.dtype)] = (
+                        px, int(gt_coord.shape[1] / 3), heatmap_out.shape[-3] // FreiHandConfig.num_joints,
+                        heatmap_out.shape[-2], heatmap_out.shape[-1], 1.0 / (b_local * world), 1.0 / denom, world,
+                        b_local, k)
                 return out
             if scaled is not None:
                 carrier = scaled
