@@ -38,6 +38,24 @@
 // overwritten.  The same chain shows that a peer's arrive for volume k+2 cannot reach an
 // mbarrier whose phase for volume k is still open.
 //
+// STREAMED shares (kMode 3): a volume that does not fit the shared memory of any cluster (fp32 96^3 =
+// 3.4 MiB) keeps the same roles, but nothing stays resident.  The ring is split in two: slots
+// [0, nslots_r) are fed from HBM (L2 evict_last) by the producer warp, reduced and handed straight
+// back by the REDUCE team; the other slots are fed by a SECOND producer warp that re-reads the same
+// stages (L2 evict_first) once the CTA's share of the volume has been reduced, and are consumed by
+// the WRITE team.  The first producer starts volume k+2 only when the write team has finished volume
+// k, so the reduction of volume k+1 runs under the gradient write of volume k and at most two
+// volumes per cluster -- (SMs / C) * 2 * vol_bytes, 106 MB for fp32 96^3 at C = 8, of which the
+// already re-read half is marked evict_first -- are live in the 126 MB L2: the second read is served
+// on chip, where the one-volume-per-cluster streaming launch (hipe_joint_loss_fused: 2 CTAs per SM,
+// 37 volumes = 131 MB in flight) re-fetched 46 % of it from HBM.
+//
+// WRAPPED visits (kWrap): when a row is not a power-of-two number of 16-byte groups (W = 96 fp32:
+// 24), whole-row visits leave a quarter of each team idle.  A stage is then KP = 3 visits of all 256
+// threads over 12 288 contiguous bytes = 32 whole rows: thread t's visit q covers group
+// (t + 256 q) mod 24 of row (t + 256 q) / 24, so its column differs per visit (kept per visit) and a
+// stage starts at y = 0, 32 or 64.
+//
 // Precision: identical contract to hipe_resident.cu (fp32 exponentials; every expectation a
 // ratio of fp64 sums built from the same rounded fp32 atoms; two atom families with their own
 // denominators: Ex = Sx/S0c, Ey = Syo/S0c + Syb/S0t, Ez = Szo/S0c + Szb/S0t).
@@ -53,6 +71,7 @@ constexpr int kNW = kC / 32;          // warps per team
 constexpr int kKP = 4;                // 16-byte vectors per thread per stage
 constexpr int kMaxSlots = 24;
 constexpr int kMaxCluster = 8;        // portable cluster size
+constexpr int kMaxClusterStr = 16;    // streamed shares: the largest (non-portable) cluster, one per GPC
 constexpr int kNSums = 7;             // S0c Sx Syo Szo S0t Syb Szb
 constexpr int kNB = 4;                // scalar records in flight (merge warp -> write team)
 constexpr int kPB = 2;                // team partials in flight (reduce team -> merge warp)
@@ -64,6 +83,9 @@ constexpr int kMaxRegs = 96;
 // Two write teams (kMode 2, 2-byte logits): 26 warps = 7 on the fullest partition -> <= 73 registers.
 constexpr int kMaxRegs2 = 72;
 constexpr int kThreads2 = 3 * kC + 64;
+// Streamed shares (kMode 3): a second producer warp for the write team's own ring.  19 warps are
+// still 5 on the fullest partition, so the 96-register cap stands.
+constexpr int kThreads3 = 2 * kC + 96;
 constexpr float kLazy = 16.f;         // lazy re-basing threshold of the online softmax
 constexpr int kSmemMax = 232448;      // 227 KB: the opt-in dynamic shared memory of one CTA
 constexpr int kMinSpare = 3;          // slots beyond one share the ring must have (look-ahead)
@@ -89,6 +111,9 @@ struct Params {
     int wteams2;      // two write teams taking alternate stages (832 threads, 72 registers)
     int sym;          // both teams reduce AND write, alternating volumes (0: team 0 reduces, team 1 writes)
     int hoist;        // H | SR: every stage starts at row y = 0 (row term = per-volume part + per-stage part)
+    int nslots_r;     // streamed shares (kMode 3): slots [0, nslots_r) feed the reduce team, the rest the write team
+    int lead;         // streamed shares: stages the first producer may run ahead of the write team (> share)
+    int pol1;         // streamed shares: L2 policy of the first read (0 normal, 1 evict_first, 2 evict_last)
     // outputs (nullable except out)
     float* coords;
     double* expect;
@@ -113,16 +138,22 @@ struct Scal {
     float pad;
 };
 
-struct Smem {
+template <int MC>
+struct SmemT {
     unsigned long long full[kMaxSlots], empty[kMaxSlots];
     unsigned long long red_ready[kPB], red_free[kPB];      // reduce team <-> merge warp
     unsigned long long scal_ready[kNB], scal_free[kNB];    // merge warp <-> write team
     unsigned long long xfull[2];                           // C remote arrivals per volume
+    unsigned long long rdone[2];                           // streamed shares: reduce team finished volume k
+    unsigned wprog, wprog_pad;                             // streamed shares: stages the write team has taken (warp 0)
     double wred[kPB][kNW][8];
     float wmax[kPB][kNW];
-    double xch[2][kMaxCluster][8];                         // [buffer][source rank][7 sums + max]
+    double xch[2][MC][8];                                  // [buffer][source rank][7 sums + max]
     Scal scal[kNB];
 };
+using Smem = SmemT<kMaxCluster>;
+using SmemStr = SmemT<kMaxClusterStr>;
+static_assert(sizeof(Smem) <= 3072, "14 slots of 16 KB + Smem must fit the 227 KB of one CTA");
 
 // Wait-time profile (diagnostic builds only, -DHIPE_CLU_PROF; scripts/diag_cluster_waits.py): lane 0
 // of every warp adds the clock cycles it spent in each class of wait, and its total run time, to a
@@ -213,6 +244,26 @@ __device__ __forceinline__ void wait_cluster(uint32_t bar, uint32_t parity) {
     }
     __trap();
 }
+// Build option (-DHIPE_CLU_PEEK=1, off): streamed shares ask one stage early, without blocking, whether
+// the next stage has landed, so that a landed stage costs no try_wait round trip in the warp's chain.
+// Measured: no difference (scripts/ab_cluster_peek.sh, two builds alternating on one box: fp32 96^3
+// 0.833-0.851 ms off, 0.809-0.856 on; fp32 64^3 streamed 0.473-0.495 off, 0.488-0.506 on).
+__device__ __forceinline__ uint32_t test_cta(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return done;
+}
+#ifndef HIPE_CLU_PEEK
+#define HIPE_CLU_PEEK 0
+#endif
 __device__ __forceinline__ uint32_t mapa(uint32_t local_saddr, uint32_t rank) {
     uint32_t remote;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_saddr), "r"(rank));
@@ -329,20 +380,28 @@ __device__ __forceinline__ double warp_sum8(const double (&v)[8], int lane) {
 // become immediates and the row bookkeeping collapses.  The launch is instruction-bound (one CTA per
 // SM, every role a dependency chain), so the instructions per stage are what is tuned.  kPass == 0
 // takes any geometry pick_geom accepts.
-template <typename T, int kPass, int kMode>
+template <typename T, int kPass, int kMode, int KP, bool kWrap>
 __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const Params p) {
     constexpr bool kSym = kMode == 1;
+    constexpr bool kStr = kMode == 3;                   // streamed shares: two rings, nothing resident
     constexpr int kWT = kMode == 2 ? 2 : 1;             // write teams
     constexpr int kTeamThreads = (1 + kWT) * kC;
+    static_assert(!kWrap || (kPass == 16 * kC), "wrapped visits: every team thread takes one vector per visit");
     using V16 = Vec16<T>;
     constexpr int VEC = V16::N;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr bool kFix = kPass != 0;
     const int pass_bytes = kFix ? kPass : p.pass_bytes;
-    const int stage_bytes = kFix ? kKP * kPass : p.stage_bytes;
-    const int slot_bytes = kFix ? kKP * kPass : p.slot_bytes;    // both specialised sizes are multiples of 128
-    const bool hoist = kFix ? true : (p.hoist != 0);       // H | SR: every stage starts at row y = 0
-    Smem& sm = *reinterpret_cast<Smem*>(smem_raw + (size_t)p.nslots * slot_bytes);
+    const int stage_bytes = kFix ? KP * kPass : p.stage_bytes;
+    const int slot_bytes = kFix ? KP * kPass : p.slot_bytes;    // the specialised sizes are multiples of 128
+    const bool hoist = kWrap ? false : (kFix ? true : (p.hoist != 0));   // H | SR: every stage starts at row y = 0
+    // streamed shares: the reduce team's ring is slots [0, nR), the write team's [nR, nR + nW)
+    const int nR = kStr ? p.nslots_r : p.nslots;
+    const int nW = kStr ? p.nslots - p.nslots_r : p.nslots;
+    const int wbase = kStr ? p.nslots_r : 0;
+    constexpr int kMC = kWrap ? kMaxClusterStr : kMaxCluster;   // (the one geometry whose volumes need 16 CTAs)
+    using SmemK = SmemT<kMC>;
+    SmemK& sm = *reinterpret_cast<SmemK*>(smem_raw + (size_t)p.nslots * slot_bytes);
     const uint32_t ring = smem_u32(smem_raw);
 
     const uint32_t C = cluster_nctarank();
@@ -372,6 +431,11 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
         // plain-store exchange: one remote arrive per peer
         mbar_init(smem_u32(&sm.xfull[0]), p.stasync ? 1 : C);
         mbar_init(smem_u32(&sm.xfull[1]), p.stasync ? 1 : C);
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(smem_u32(&sm.rdone[s]), kNW);
+        }
+        sm.wprog = 0;
         mbar_fence_init();
         fence_proxy_async();
     }
@@ -382,6 +446,32 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
     const long long prof_start_ = clock64();
     unsigned long long prof_acc_[3] = {0ull, 0ull, 0ull};
 #endif
+
+    if (kStr && threadIdx.x >= kTeamThreads + 64) {
+        // -------------------- second producer warp (streamed shares) --------------------
+        // Re-reads the share for the write team, from L2: volume k's stages are requested only after
+        // this CTA's reduce team has consumed them all (rdone), and as far ahead of the write team as
+        // its ring allows -- the prefetch runs under the cross-CTA merge of the volume.
+        if ((threadIdx.x & 31) == 0) {
+            const uint64_t pol = policy_evict_first();
+            Ring r;
+            r.init();
+            for (long long k = 0; k < nv; ++k) {
+                const long long vol = cluster_id + k * p.n_clusters;
+                const unsigned char* src = p.in + vol * p.vol_bytes + (long long)sv0 * stage_bytes;
+                wait_cta(smem_u32(&sm.rdone[k & 1]), (uint32_t)(k >> 1) & 1);
+                for (int s = 0; s < nst; ++s) {
+                    if (r.lap > 0) wait_cta(smem_u32(&sm.empty[wbase + r.slot]), (r.lap - 1) & 1);
+                    const uint32_t bar = smem_u32(&sm.full[wbase + r.slot]);
+                    mbar_arrive_expect_tx(bar, (uint32_t)stage_bytes);
+                    tma_load_1d(ring + (uint32_t)wbase * (uint32_t)slot_bytes + r.off, src, (uint32_t)stage_bytes, bar, pol);
+                    src += stage_bytes;
+                    r.next(nW, slot_bytes);
+                }
+            }
+        }
+        return;
+    }
 
     if (threadIdx.x >= kTeamThreads + 32) {
         // ------------------------------- merge warp -------------------------------
@@ -446,20 +536,20 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
             CLU_WAIT(4, wait_cluster(smem_u32(&sm.xfull[xb]), (uint32_t)(k >> 1) & 1));
             CLU_TRACE(k, 6);
             // all loads first (independent), then the short dependent chains
-            float mr[kMaxCluster];
-            double vr[kMaxCluster];
+            float mr[kMC];
+            double vr[kMC];
 #pragma unroll
-            for (int r = 0; r < kMaxCluster; ++r) {
+            for (int r = 0; r < kMC; ++r) {
                 const bool on = (uint32_t)r < C;
                 mr[r] = on ? (float)sm.xch[xb][r][kNSums] : kNegInf;
                 vr[r] = on ? sm.xch[xb][r][li] : 0.0;
             }
             float M = mr[0];
 #pragma unroll
-            for (int r = 1; r < kMaxCluster; ++r) M = fmaxf(M, mr[r]);
+            for (int r = 1; r < kMC; ++r) M = fmaxf(M, mr[r]);
             double a = 0.0;
 #pragma unroll
-            for (int r = 0; r < kMaxCluster; ++r) a = fma((double)rebase_w(mr[r], M), vr[r], a);
+            for (int r = 0; r < kMC; ++r) a = fma((double)rebase_w(mr[r], M), vr[r], a);
             // loss.py:39-41 (expectations) and :54-56 (normalisation), in fp64, rounded once.
             // Lane t (< 3) finishes axis t: x, y, z.  Sums: 0 S0c 1 Sx 2 Syo 3 Szo 4 S0t 5 Syb 6 Szb.
             const double a0 = __shfl_sync(0xffffffffu, a, 0), a4 = __shfl_sync(0xffffffffu, a, 4);
@@ -495,13 +585,29 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
     if (threadIdx.x >= kTeamThreads) {
         // ------------------------------- producer warp -------------------------------
         if ((threadIdx.x & 31) == 0) {
-            const uint64_t pol = policy_evict_first();
+            // streamed shares: the lines are wanted again within two volumes' time
+            const uint64_t pol = !kStr || p.pol1 == 1 ? policy_evict_first()
+                                                      : (p.pol1 == 2 ? policy_evict_last() : policy_evict_normal());
             Ring r;
             r.init();
             for (long long k = 0; k < nv; ++k) {
                 const long long vol = cluster_id + k * p.n_clusters;
                 const unsigned char* src = p.in + vol * p.vol_bytes + (long long)sv0 * stage_bytes;
                 for (int s = 0; s < nst; ++s) {
+                    if constexpr (kStr) {
+                        // Streamed shares: stay at most `lead` stages ahead of the write team -- what has
+                        // been read once and not yet again is what the L2 must hold (lead x stage bytes x
+                        // CTAs).  lead > share, so the wait only ever concerns volumes whose reduction
+                        // needs nothing more from this warp: no cycle.
+                        const unsigned q0 = (unsigned)(k * nst + s);
+                        if (q0 >= (unsigned)p.lead) {
+                            unsigned spin = 0;
+                            while ((int)(*(volatile unsigned*)&sm.wprog + (unsigned)p.lead - q0) <= 0) {
+                                __nanosleep(100);
+                                if (++spin > (1u << 26)) __trap();
+                            }
+                        }
+                    }
                     if (r.lap > 0) CLU_WAIT(0, wait_cta(smem_u32(&sm.empty[r.slot]), (r.lap - 1) & 1));
                     if (s == 0) CLU_TRACE(k, 0);
                     if (s == nst - 1) CLU_TRACE(k, 1);
@@ -509,7 +615,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
                     mbar_arrive_expect_tx(bar, (uint32_t)stage_bytes);
                     tma_load_1d(ring + r.off, src, (uint32_t)stage_bytes, bar, pol);
                     src += stage_bytes;
-                    r.next(p.nslots, slot_bytes);
+                    r.next(nR, slot_bytes);
                 }
             }
         }
@@ -529,6 +635,9 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
     const int zb0 = rowbase0 / p.H, yb0 = rowbase0 - zb0 * p.H;
     const uint32_t lds_base = ring + 16u * tid;
 
+    // streamed shares: has the next stage of this team's ring landed already?  (asked one stage early)
+    constexpr bool kPeek = kStr && HIPE_CLU_PEEK;
+    uint32_t peek = 0;
     // =============================== reduction of one volume ===============================
     // (the team's share of volume k: the stages at ring position r, which is advanced past them)
     auto reduce_volume = [&](long long k, Ring& r) {
@@ -536,24 +645,33 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
             const double dzd = (double)(p.SR / p.H);      // hoist: z advance per stage
             const unsigned sb = (unsigned)(k % kPB);
             float m = kNegInf, mL = kNegInf, tm = kNegInf;   // offset in use, fl(m*log2e), true maximum
-            float2 c2[kKP][VEC / 2];
+            float2 c2[KP][VEC / 2];
 #pragma unroll
-            for (int q = 0; q < kKP; ++q)
+            for (int q = 0; q < KP; ++q)
 #pragma unroll
                 for (int j = 0; j < VEC / 2; ++j) c2[q][j] = make_float2(0.f, 0.f);
             double s0t = 0.0, syb = 0.0, szb = 0.0;
             int zb = zb0, yb = yb0;                 // general geometry
             double zbd = (double)zb0;               // hoist: the stage's first z as a double, y is 0
-            auto fetch = [&](uint4 (&dst)[kKP]) {
-                CLU_WAIT(1, wait_cta(smem_u32(&sm.full[r.slot]), r.lap & 1));
+            auto fetch = [&](uint4 (&dst)[KP]) {
+                if (!(kPeek && peek)) CLU_WAIT(1, wait_cta(smem_u32(&sm.full[r.slot]), r.lap & 1));
                 if (active) {
                     const uint32_t sbase = lds_base + r.off;
 #pragma unroll
-                    for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * pass_bytes);
+                    for (int q = 0; q < KP; ++q) dst[q] = lds128(sbase + q * pass_bytes);
                 }
-                r.next(p.nslots, slot_bytes);
+                if constexpr (kStr) {
+                    // streamed shares: nothing stays resident -- the slot goes back to the producer as
+                    // soon as the loads have returned
+                    uint32_t dep = 0;
+#pragma unroll
+                    for (int q = 0; q < KP; ++q) dep ^= dst[q].x;
+                    if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.empty[r.slot]), active ? dep : 0u);
+                }
+                r.next(nR, slot_bytes);
+                if constexpr (kPeek) peek = test_cta(smem_u32(&sm.full[r.slot]), r.lap & 1);   // the stage after this one
             };
-            auto compute = [&](const uint4 (&raw)[kKP]) {
+            auto compute = [&](const uint4 (&raw)[KP]) {
                 if (active) {
                     // the stage's maximum straight from the raw words (2-byte logits: packed bf16x2
                     // maxima, half the instructions and nothing unpacked yet)
@@ -561,7 +679,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
                     if constexpr (VEC == 8) {
                         __nv_bfloat162 mx = u32_as_bf162(raw[0].x);
 #pragma unroll
-                        for (int q = 0; q < kKP; ++q) {
+                        for (int q = 0; q < KP; ++q) {
                             mx = __hmax2(mx, __hmax2(__hmax2(u32_as_bf162(raw[q].x), u32_as_bf162(raw[q].y)),
                                                      __hmax2(u32_as_bf162(raw[q].z), u32_as_bf162(raw[q].w))));
                         }
@@ -569,7 +687,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
                     } else {
                         smax = kNegInf;
 #pragma unroll
-                        for (int q = 0; q < kKP; ++q)
+                        for (int q = 0; q < KP; ++q)
                             smax = fmaxf(smax, fmaxf(fmaxf(__uint_as_float(raw[q].x), __uint_as_float(raw[q].y)),
                                                      fmaxf(__uint_as_float(raw[q].z), __uint_as_float(raw[q].w))));
                     }
@@ -580,7 +698,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
                         const float f = rebase_w(m, smax);
                         const float2 f2 = make_float2(f, f);
 #pragma unroll
-                        for (int q = 0; q < kKP; ++q)
+                        for (int q = 0; q < KP; ++q)
 #pragma unroll
                             for (int j = 0; j < VEC / 2; ++j) c2[q][j] = __fmul2_rn(c2[q][j], f2);
                         const double fd = (double)f;
@@ -593,7 +711,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
                     const float2 noff2 = make_float2(noff, noff), l2e2 = make_float2(kLog2e, kLog2e);
                     float2 rs2 = make_float2(0.f, 0.f);
 #pragma unroll
-                    for (int q = 0; q < kKP; ++q) {
+                    for (int q = 0; q < KP; ++q) {
                         float v[VEC];
                         V16::unpack(raw[q], v);
                         float2 e2[VEC / 2];
@@ -628,7 +746,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
             // dependency chains overlap in every warp.
             // (4-byte logits only: with 8 elements per vector the second buffer spills.)
             if constexpr (VEC == 4) {
-                uint4 rawA[kKP], rawB[kKP];
+                uint4 rawA[KP], rawB[KP];
                 fetch(rawA);
                 for (int s = 0; s < nst; s += 2) {
                     if (s + 1 < nst) fetch(rawB);
@@ -639,11 +757,15 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
                     }
                 }
             } else {
-                uint4 rawA[kKP];
+                uint4 rawA[KP];
                 for (int s = 0; s < nst; ++s) {
                     fetch(rawA);
                     compute(rawA);
                 }
+            }
+            if constexpr (kStr) {
+                // the whole share has been requested and consumed: the second producer may re-read it
+                if (lane == 0) mbar_arrive(smem_u32(&sm.rdone[k & 1]));
             }
             if (warp == 0) CLU_TRACE(k, 2);
             // ---- fold the thread's accumulators, sum over the warp, hand to the merge warp ----
@@ -655,24 +777,29 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) col[j] = 0.0;
 #pragma unroll
-                for (int q = 0; q < kKP; ++q) {
+                for (int q = 0; q < KP; ++q) {
                     // row offsets of this thread's visit q inside a stage
-                    const int rho = rr + q * p.R;
+                    const int rho = kWrap ? (tid + q * kC) / p.G : rr + q * p.R;
                     const int zo = rho / p.H, yo = rho - zo * p.H;
+                    const int xq = kWrap ? ((tid + q * kC) % p.G) * VEC : x0;   // wrapped visits: the column moves too
                     double row = 0.0;
 #pragma unroll
                     for (int j = 0; j < VEC; ++j) {
                         const double cd = widen_nonneg((j & 1) ? c2[q][j / 2].y : c2[q][j / 2].x);
                         row += cd;
-                        col[j] += cd;
+                        if constexpr (kWrap) q8[1] = fma((double)(xq + j), cd, q8[1]);
+                        else col[j] += cd;
                     }
+                    if constexpr (kWrap) q8[0] += row;
                     q8[2] = fma((double)yo, row, q8[2]);
                     q8[3] = fma((double)zo, row, q8[3]);
                 }
+                if constexpr (!kWrap) {
 #pragma unroll
-                for (int j = 0; j < VEC; ++j) {
-                    q8[0] += col[j];
-                    q8[1] = fma((double)(x0 + j), col[j], q8[1]);
+                    for (int j = 0; j < VEC; ++j) {
+                        q8[0] += col[j];
+                        q8[1] = fma((double)(x0 + j), col[j], q8[1]);
+                    }
                 }
                 q8[4] = s0t; q8[5] = syb; q8[6] = szb;
             }
@@ -692,12 +819,13 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
     };
 
     // ============================== gradient write of one volume ==============================
+    unsigned wcount = 0;
     auto write_volume = [&](long long k, Ring& r) {
         // row offsets of this thread's kKP visits inside a stage, as exact small floats
-        float yof[kKP], zof[kKP];
+        float yof[KP], zof[KP];
 #pragma unroll
-        for (int q = 0; q < kKP; ++q) {
-            const int rho = rr + q * p.R;
+        for (int q = 0; q < KP; ++q) {
+            const int rho = kWrap ? (tid + q * kC) / p.G : rr + q * p.R;
             const int zo = rho / p.H;
             zof[q] = (float)zo;
             yof[q] = (float)(rho - zo * p.H);
@@ -740,46 +868,64 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
             if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.scal_free[rb]), dep);
         }
         const float2 nML2 = make_float2(-ML, -ML);
-        float2 ax2[VEC / 2];
+        // column terms kx (x - Ex): one set per thread, or one per visit when the visits wrap
+        constexpr int kAX = kWrap ? KP : 1;
+        float2 ax2[kAX][VEC / 2];
 #pragma unroll
-        for (int j = 0; j < VEC / 2; ++j)
-            ax2[j] = make_float2((float)(kxd * ((double)(x0 + 2 * j) - Ex)), (float)(kxd * ((double)(x0 + 2 * j + 1) - Ex)));
+        for (int q = 0; q < kAX; ++q) {
+            const int xq = kWrap ? ((tid + q * kC) % p.G) * VEC : x0;
+#pragma unroll
+            for (int j = 0; j < VEC / 2; ++j)
+                ax2[q][j] = make_float2((float)(kxd * ((double)(xq + 2 * j) - Ex)), (float)(kxd * ((double)(xq + 2 * j + 1) - Ex)));
+        }
         // (idx - E) must keep its ABSOLUTE accuracy: E split into hi + lo floats, the row index an
         // exact small float, so (y - Eh) is exact near the peak and - El restores the rest
         const float Eyh = (float)Ey, Eyl = (float)(Ey - (double)Eyh);
         const float Ezh = (float)Ez, Ezl = (float)(Ez - (double)Ezh);
         // hoist (every stage starts at y = 0): the visit's row term is A[q] + B(stage),
         //   A[q] = ky (yo_q - Ey) + kz zo_q      per volume,     B = kz (z_stage - Ez)   per stage
-        float rowA[kKP];
+        float rowA[KP];
 #pragma unroll
-        for (int q = 0; q < kKP; ++q) rowA[q] = fmaf(kz, zof[q], ky * ((yof[q] - Eyh) - Eyl));
+        for (int q = 0; q < KP; ++q) rowA[q] = fmaf(kz, zof[q], ky * ((yof[q] - Eyh) - Eyl));
         float ybf = (float)yb0, zbf = (float)zb0;
         unsigned char* gdst = p.out + vol * p.vol_bytes + (long long)sv0 * stage_bytes + 16ll * tid;
 
-        auto fetch = [&](uint4 (&dst)[kKP]) {
+        auto fetch = [&](uint4 (&dst)[KP]) {
             // The stage landed long ago: the reduce team observed its `full` barrier, and the chain
             // reduce team -> red_ready -> merge warp -> scal_ready -> this thread (each an mbarrier
             // release / acquire pair) orders the TMA's bytes before these loads.  Re-checking the
             // barrier here cost 14 % of the write team's time.
+            // (Streamed shares: the slot is this team's own re-read, so its barrier is the only order.)
+            if constexpr (kStr) {
+                if (!(kPeek && peek)) CLU_WAIT(7, wait_cta(smem_u32(&sm.full[wbase + r.slot]), r.lap & 1));
+            }
             if (active) {
-                const uint32_t sbase = lds_base + r.off;
+                const uint32_t sbase = lds_base + (uint32_t)wbase * (uint32_t)slot_bytes + r.off;
 #pragma unroll
-                for (int q = 0; q < kKP; ++q) dst[q] = lds128(sbase + q * pass_bytes);
+                for (int q = 0; q < KP; ++q) dst[q] = lds128(sbase + q * pass_bytes);
             }
             // the slot goes back to the producer only once the loads have RETURNED
             uint32_t dep = 0;
 #pragma unroll
-            for (int q = 0; q < kKP; ++q) dep ^= dst[q].x;
-            if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.empty[r.slot]), active ? dep : 0u);
-            r.next(p.nslots, slot_bytes);
+            for (int q = 0; q < KP; ++q) dep ^= dst[q].x;
+            if (lane == 0) mbar_arrive_after_loads(smem_u32(&sm.empty[wbase + r.slot]), active ? dep : 0u);
+            if constexpr (kStr) {
+                // progress of the write team, for the first producer's throttle (a pace, not an order)
+                if (warp == 0 && lane == 0) *(volatile unsigned*)&sm.wprog = ++wcount;
+            }
+            r.next(nW, slot_bytes);
+            if constexpr (kPeek) peek = test_cta(smem_u32(&sm.full[wbase + r.slot]), r.lap & 1);
         };
-        auto compute = [&](const uint4 (&raw)[kKP]) {
+        auto compute = [&](const uint4 (&raw)[KP]) {
             if (active) {
                 const float dzs = (zbf - Ezh) - Ezl;             // z_stage - Ez, absolute accuracy kept
+                const float kzt = kz * dzs;                      // wrapped visits: a stage lies in one z
 #pragma unroll
-                for (int q = 0; q < kKP; ++q) {
+                for (int q = 0; q < KP; ++q) {
                     float rtv;
-                    if (hoist) {
+                    if (kWrap) {
+                        rtv = fmaf(ky, ((ybf + yof[q]) - Eyh) - Eyl, kzt);
+                    } else if (hoist) {
                         rtv = fmaf(kz, dzs, rowA[q]);
                     } else {
                         const float y = ybf + yof[q], z = zbf + zof[q];
@@ -791,7 +937,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
 #pragma unroll
                     for (int j = 0; j < VEC / 2; ++j) {
                         const float2 a2 = __ffma2_rn(make_float2(v[2 * j], v[2 * j + 1]), l2e2, nML2);
-                        const float2 w2 = __fadd2_rn(ax2[j], rt2);
+                        const float2 w2 = __fadd2_rn(ax2[kWrap ? q : 0][j], rt2);
                         float2 e2;
 #if HIPE_CLU_POLY
                         if (VEC == 8 && (HIPE_CLU_POLY == 2 || (q & 1))) e2 = ex2_poly2(a2);
@@ -814,7 +960,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
             }
         };
         if constexpr (kWT == 1) {
-            uint4 rawA[kKP], rawB[kKP];
+            uint4 rawA[KP], rawB[KP];
             fetch(rawA);
             for (int s = 0; s < nst; s += 2) {
                 if (s + 1 < nst) fetch(rawB);
@@ -826,7 +972,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
             }
         } else {
             // two write teams: alternate stages of the same volume (each frees the slots it wrote)
-            uint4 rawA[kKP];
+            uint4 rawA[KP];
             for (int s = 0; s < nst; ++s) {
                 if ((s & 1) == wt) {
                     fetch(rawA);
@@ -846,6 +992,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
         if (warp == 0) CLU_TRACE(k, 9);
     };
 
+    // (wcount: stages write warp 0 has taken so far, all volumes)
     // Team roles.  kMode 0 (what ships): team 0 reduces every volume, team 1 writes every volume.
     // Two other layouts were built to relieve the 2-byte gradient pass (the write team is > 90 % busy
     // there) and both lost on every shape; they compile only with -DHIPE_CLU_EXPERIMENTS and are
@@ -905,7 +1052,13 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
 // ---------------------------------------------------------------------------------------
 struct Geom {
     int G, R, SR, stage_bytes, pass_bytes, nact, NSv, slot_bytes, nslots, C, max_share;
+    int wrap;        // wrapped visits: stages of 3 x 4096 bytes = whole rows (W = 96 fp32)
+    int streamed;    // the share does not fit the ring: two rings, second read through L2
+    int nslots_r;    // streamed: slots of the reduce team's ring
+    int lead;        // streamed: stages the first read may run ahead of the second (0: resident form)
 };
+constexpr int kWrapKP = 3;
+constexpr int kStrMargin = 13;   // streamed shares: default lead = share + this many stages
 
 static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) {
     const int esz = dtype == HIPE_F32 ? 4 : 2;
@@ -915,7 +1068,26 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
     const long long NR = (long long)D * H;
     if (NR >= (1ll << 30)) return false;
     bool found = false;
-    for (int R = kC / G; R >= 1; --R) {
+    g->wrap = 0; g->streamed = 0; g->nslots_r = 0; g->lead = 0;
+    // Wrapped visits: whole-row visits would idle part of each team (R * G < 256) but 3 visits of all
+    // 256 threads are a whole number of rows that divides H (a stage never straddles two z).
+    {
+        const long long sb = (long long)kWrapKP * kC * 16;
+        const long long nsv = (sb % row_b == 0) ? NR / (sb / row_b) : 0;
+        const long long ring = (kSmemMax - (long long)sizeof(Smem)) / sb;
+        // (built for 4-byte logits and streamed shares only: the one shape that needs it is fp32 96^3)
+        if (dtype == HIPE_F32 && kC % G != 0 && sb % row_b == 0 && H % (sb / row_b) == 0 &&
+            (nsv + kMaxCluster - 1) / kMaxCluster + kMinSpare > ring && !getenv("HIPE_CLUSTER_GENERIC")) {
+            g->G = G; g->R = 0; g->SR = (int)(sb / row_b);
+            g->pass_bytes = kC * 16;
+            g->stage_bytes = (int)sb;
+            g->nact = kC;
+            g->NSv = (int)(NR / g->SR);
+            g->wrap = 1;
+            found = true;
+        }
+    }
+    for (int R = kC / G; R >= 1 && !found; --R) {
         const int SR = kKP * R;
         if (2 * R * G < kC) break;   // fewer than half the team would work
         const bool ok = (SR % H == 0 && NR % SR == 0) || (H % SR == 0);
@@ -963,16 +1135,68 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
         }
     }
     (void)n_vol;
-    return g->C > 0;
+    // Streamed shares (two rings, second read through L2).  Any cluster size works, nothing is resident;
+    // what matters is what the L2 must hold between the two reads: `lead` stages per CTA = one volume
+    // per cluster + kStrMargin stages per CTA.  Measured with ncu (fp32, DRAM read bytes / algorithmic):
+    // 64^3 C=8 (41 MB) 1.03, C=6 (52 MB) 1.21, C=4 (63 MB) 1.42; 96^3 C=8 lead 37 (55 MB) 1.40, the same
+    // on 12 / 9 clusters (47 / 35 MB) 1.14 / 1.01, C=16 lead 31 (43 MB) 1.03: about 40 MB of the 126 MB L2
+    // serve this pattern.  So: 8 CTAs if that fits 44 MB, else 16 (one cluster per GPC, 112 SMs).
+    // Taken when no cluster can hold the volume, and -- because the two rings decouple the teams, which
+    // is worth more than the 12 SMs a cluster of 8 leaves idle -- for 4-byte volumes of the 4096-byte
+    // geometry with shares of >= 8 stages that fit the 44 MB at C = 8 (fp32 64^3 x 1344, same box,
+    // alternating: 0.473-0.495 ms streamed vs 0.500-0.518 resident; x 672: 0.257 vs 0.269).  It loses
+    // where the share is short or the gradient pass is XU-bound (bf16 64^3 x 2688: 0.60 vs 0.54; fp32
+    // 56^3 x 672: 0.190-0.205 vs 0.187-0.192; fp32 32^3 x 5376: 0.264 vs 0.242).
+    // HIPE_CLUSTER_STREAM=1 / 0 forces / forbids it.
+    const long long vol_bytes = NR * row_b;
+    const double mb8 = (15.0 * (double)vol_bytes + 120.0 * kStrMargin * g->stage_bytes) / 1e6;
+    {
+        int force = -1;
+        if (const char* env = getenv("HIPE_CLUSTER_STREAM")) force = atoi(env);
+        const bool prefer = esz == 4 && g->stage_bytes == kKP * kC * 16 && g->nact == kC && g->SR % H == 0 &&
+                            g->NSv >= 8 * kMaxCluster && mb8 <= 44.0 && !want;
+        if (g->C > 0 && (force == 0 || (force < 0 && !prefer))) return true;
+        if (g->C == 0 && force == 0) return false;
+    }
+    nslots = (int)((kSmemMax - (int)(g->wrap ? sizeof(SmemStr) : sizeof(Smem))) / g->slot_bytes);
+    if (nslots > kMaxSlots) nslots = kMaxSlots;
+    if (const char* env = getenv("HIPE_CLUSTER_SLOTS")) {
+        const int v = atoi(env);
+        if (v >= 6 && v < nslots) nslots = v;
+    }
+    if (nslots < 6) return false;
+    g->nslots = nslots;
+    const int maxC = g->wrap ? kMaxClusterStr : kMaxCluster;     // (16-CTA exchange buffers: wrapped kernel only)
+    int C = (mb8 <= 44.0) ? kMaxCluster : maxC;
+    if (want >= 1 && want <= maxC) C = want;
+    while (C > 1 && g->NSv < C) --C;
+    g->C = C;
+    g->max_share = (g->NSv + C - 1) / C;
+    g->streamed = 1;
+    g->nslots_r = (nslots * 5 + 4) / 9;          // HBM latency on the reduce ring, L2 latency on the other
+    if (const char* env = getenv("HIPE_CLUSTER_RSLOTS")) {
+        const int v = atoi(env);
+        if (v >= 2 && v <= nslots - 2) g->nslots_r = v;
+    }
+    g->lead = g->max_share + kStrMargin;
+    if (const char* env = getenv("HIPE_CLUSTER_LEAD")) {
+        const int v = atoi(env);
+        if (v > g->max_share) g->lead = v;
+    }
+    return true;
 }
 
-template <typename T, int kPass, int kMode>
+template <typename T, int kPass, int kMode, int KP = kKP, bool kWrap = false>
 static int launch(const Params& p0, const Geom& g, cudaStream_t st) {
-    auto kern = k_cluster<T, kPass, kMode>;
-    constexpr int kBlock = kMode == 2 ? kThreads2 : kThreads;
-    const size_t smem = (size_t)g.nslots * g.slot_bytes + sizeof(Smem);
+    auto kern = k_cluster<T, kPass, kMode, KP, kWrap>;
+    constexpr int kBlock = kMode == 2 ? kThreads2 : (kMode == 3 ? kThreads3 : kThreads);
+    const size_t smem = (size_t)g.nslots * g.slot_bytes + (kWrap ? sizeof(SmemStr) : sizeof(Smem));
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
+    if (g.C > kMaxCluster) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e != cudaSuccess) return (int)e;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.blockDim = dim3(kBlock, 1, 1);
     cfg.dynamicSmemBytes = smem;
@@ -1034,7 +1258,7 @@ extern "C" long long hipe_cluster_workspace_bytes(int dtype, long long n_vol, in
 }
 
 extern "C" int hipe_cluster_plan(int dtype, long long n_vol, int D, int H, int W, int* cluster, int* nslots,
-                                 int* share_stages, int* stage_bytes) {
+                                 int* share_stages, int* stage_bytes, int* lead_stages) {
     clu::Geom g;
     if ((dtype != HIPE_F32 && dtype != HIPE_BF16) || n_vol <= 0 || D <= 0 || H <= 0 || W <= 0 ||
         !clu::pick_geom(dtype, n_vol, D, H, W, &g))
@@ -1043,6 +1267,7 @@ extern "C" int hipe_cluster_plan(int dtype, long long n_vol, int D, int H, int W
     if (nslots) *nslots = g.nslots;
     if (share_stages) *share_stages = g.max_share;
     if (stage_bytes) *stage_bytes = g.stage_bytes;
+    if (lead_stages) *lead_stages = g.streamed ? g.lead : 0;
     return 0;
 }
 
@@ -1080,6 +1305,10 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     p.W = W; p.H = H; p.D = D;
     p.G = g.G; p.R = g.R; p.SR = g.SR; p.stage_bytes = g.stage_bytes; p.pass_bytes = g.pass_bytes;
     p.nact = g.nact; p.NSv = g.NSv; p.nslots = g.nslots; p.slot_bytes = g.slot_bytes;
+    p.nslots_r = g.nslots_r;
+    p.lead = g.lead;
+    p.pol1 = 2;
+    if (const char* env = getenv("HIPE_CLUSTER_POL1")) p.pol1 = atoi(env);
     p.coords = coords; p.expect = expect; p.stats = stats; p.loss_terms = loss_terms;
     p.gt = gt; p.vis = vis; p.tgt_f64 = (tgt_dtype == HIPE_F64); p.norm = norm;
     p.ticket = static_cast<unsigned*>(workspace);
@@ -1109,6 +1338,14 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     if (mode == 1) return dtype == HIPE_F32 ? HIPE_CLU_LAUNCH(float, 1) : HIPE_CLU_LAUNCH(__nv_bfloat16, 1);
     if (mode == 2) return dtype == HIPE_F32 ? HIPE_CLU_LAUNCH(float, 2) : HIPE_CLU_LAUNCH(__nv_bfloat16, 2);
 #endif
+    if (g.streamed) {
+        // streamed shares: the wrapped fp32 geometry (W = 96), the two specialised whole-row ones, or any
+        if (g.wrap) {
+            if (dtype != HIPE_F32) return HIPE_E_UNSUPPORTED;
+            return clu::launch<float, 16 * clu::kC, 3, clu::kWrapKP, true>(p, g, st);
+        }
+        return dtype == HIPE_F32 ? HIPE_CLU_LAUNCH(float, 3) : HIPE_CLU_LAUNCH(__nv_bfloat16, 3);
+    }
     return dtype == HIPE_F32 ? HIPE_CLU_LAUNCH(float, 0) : HIPE_CLU_LAUNCH(__nv_bfloat16, 0);
 #undef HIPE_CLU_LAUNCH
 }

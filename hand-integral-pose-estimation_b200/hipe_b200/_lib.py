@@ -30,7 +30,7 @@ SIGNATURES = {
     "hipe_joint_loss_resident": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp, _vp,
                                       _vp, _ll, _vp]),
     "hipe_cluster_workspace_bytes": (_ll, [_i, _ll, _i, _i, _i]),
-    "hipe_cluster_plan": (_i, [_i, _ll, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "hipe_cluster_plan": (_i, [_i, _ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "hipe_joint_loss_cluster": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp, _vp,
                                      _vp, _ll, _vp]),
     "hipe_scale_inplace": (_i, [_vp, _i, _ll, _vp, _vp]),

@@ -216,16 +216,19 @@ def fused_plan(logits, n_vol, D, H, W):
 def _fused_plan(logits, n_vol, D, H, W):
     """Which launch computes loss + gradient fastest for this geometry, from same-box B200 A/Bs
     (profiles/r2_configs.md):
-      "cluster"  the cluster-resident launch (hipe_joint_loss_cluster: every volume held in the
-                 distributed shared memory of one thread-block cluster, one HBM read + one write,
-                 nothing in L2) for the geometries its loops are specialised for -- 4096- or
-                 3136-byte visits with every stage starting at y = 0, i.e. 64^3 and 32^3 in fp32 and
-                 bf16, 56^3 in fp32 (x 672: 0.177 ms vs 0.202 stream; x 2016: 0.530 vs 0.576): fp32 64^3 x 1344 0.482-0.497 ms vs 0.540 resident / 0.556-0.572 stream, x 672
-                 0.265 vs 0.301; bf16 64^3 x 10752 2.09 vs 2.40 stream, x 1344 0.273 vs 0.331; fp32 32^3 x
-                 5376 0.244 vs 0.282; bf16 32^3 (64 KiB volumes) x 5376 0.162 vs 0.224 stream / 0.248 pair;
-      "stream"   one launch whose second read goes through L2 (hipe_joint_loss_fused) for every other
-                 fp32 / bf16 volume >= 128 KiB (fp32 48^3 x 2016: 0.362 vs 0.42 cluster, 96^3 does not
-                 fit a cluster);
+      "cluster"  the cluster launch (hipe_joint_loss_cluster: one HBM read + one write per volume) for
+                 the geometries its loops are specialised for.  Resident form (the volume stays in the
+                 cluster's shared memory, nothing in L2) -- 4096- or 3136-byte visits with every stage
+                 starting at y = 0: bf16 64^3 x 10752 2.09 ms vs 2.40 stream, x 1344 0.273 vs 0.331;
+                 fp32 56^3 x 672 0.177 vs 0.202, x 2016 0.530 vs 0.576; fp32 32^3 x 5376 0.244 vs 0.282;
+                 bf16 32^3 (64 KiB volumes) x 5376 0.162 vs 0.224 stream / 0.248 pair.  Streamed form (two
+                 rings, second read through L2 a bounded lead behind): fp32 64^3 x 1344 0.473-0.495 vs
+                 0.500-0.518 resident form / 0.540 resident launch / 0.556-0.572 stream, x 672 0.257 vs
+                 0.269 / 0.301; fp32 96^3 (fits no cluster; wrapped 12 KiB stages on 16 CTAs) x 672
+                 0.81-0.85 vs 0.99-1.02 stream;
+      "stream"   one launch whose second read goes through L2 unbounded (hipe_joint_loss_fused) for
+                 every other fp32 / bf16 volume >= 128 KiB (fp32 48^3 x 2016: 0.362 vs 0.42 cluster; the
+                 general-geometry streamed cluster form is untuned);
       None       the two-launch forward + recompute backward, which still wins on tiny volumes (fp32
                  16^3: 0.366 ms vs 0.433 fused; bf16 32^3 is a tie).
     "resident" (hipe_joint_loss_resident, the L2-window launch that was the fp32 64^3 default before
@@ -237,11 +240,15 @@ def _fused_plan(logits, n_vol, D, H, W):
     if vol_bytes >= (1 << 16) and n_vol >= 8:
         cp = cluster_plan(logits, n_vol, D, H, W)
         if cp is not None:
-            stage_bytes, row_bytes = cp[3], W * esz
+            stage_bytes, lead, row_bytes = cp[3], cp[4], W * esz
             sr = stage_bytes // row_bytes                       # rows per stage
             # the specialised loops; 2-byte 56^3 (12.25 KB stages on 2 CTAs) is the one case among them
             # where the stream launch is still ahead (bf16 56^3 x 2016: 0.328 ms vs 0.366)
-            if sr % H == 0 and (stage_bytes == 16384 or (stage_bytes == 12544 and esz == 4)):
+            if sr % H == 0 and (stage_bytes == 16384 or (stage_bytes == 12544 and esz == 4)) and \
+                    (lead == 0 or (esz == 4 and lead * stage_bytes * 120 <= 46e6)):      # streamed: the L2 must hold it
+                return "cluster"
+            # wrapped visits (fp32 rows of 24 vectors): 3 x 4096-byte visits = 32 whole rows
+            if lead > 0 and esz == 4 and stage_bytes == 12288 and row_bytes == 384:
                 return "cluster"
     if (W * esz) % 16 == 0 and vol_bytes >= (1 << 17):
         return "stream"
@@ -287,13 +294,15 @@ def resident_timed_out(device, n_vol):
 
 
 def cluster_plan(logits, n_vol, D, H, W):
-    """(cluster size, ring slots per CTA, stages per CTA share, bytes per stage) of the
-    cluster-resident launch for this geometry, or None when it cannot take it."""
+    """(cluster size, ring slots per CTA, stages per CTA share, bytes per stage, lead) of the cluster
+    launch for this geometry, or None when it cannot take it.  lead = 0: the volume stays resident in
+    the cluster's shared memory; lead > 0: streamed shares, the second read comes through L2 at most
+    that many stages behind the first."""
     import ctypes
-    c, ns, sh, sb = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    c, ns, sh, sb, ld = (ctypes.c_int() for _ in range(5))
     rc = _lib.load().hipe_cluster_plan(_logits_code(logits), n_vol, D, H, W, ctypes.byref(c), ctypes.byref(ns),
-                                       ctypes.byref(sh), ctypes.byref(sb))
-    return None if rc != 0 else (c.value, ns.value, sh.value, sb.value)
+                                       ctypes.byref(sh), ctypes.byref(sb), ctypes.byref(ld))
+    return None if rc != 0 else (c.value, ns.value, sh.value, sb.value, ld.value)
 
 
 def cluster_supported(logits, n_vol, D, H, W):

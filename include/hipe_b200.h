@@ -152,20 +152,24 @@ HIPE_API int hipe_joint_loss_resident(const void* logits_dev, int dtype, long lo
                              void* stream);
 
 /*
- * The same contract again, as ONE persistent launch of thread-block CLUSTERS that hold each volume
- * in distributed shared memory between the reduction and the gradient write (C CTAs x up to 14
- * 16 KB TMA slots; the C partial sums travel CTA to CTA through st.shared::cluster + remote
- * mbarrier arrives): HBM sees each volume once in and its gradient once out, the L2 holds nothing,
- * and no role waits on global memory.  Takes every geometry whose volume fits one cluster's
- * shared memory with look-ahead to spare (fp32 64^3 on 8 CTAs, bf16 64^3 and fp32 56^3 on 4).
+ * The same contract again, as ONE persistent launch of thread-block CLUSTERS (C CTAs x up to 14
+ * 16 KB TMA slots; the C partial sums travel CTA to CTA through st.async into distributed shared
+ * memory): HBM sees each volume once in and its gradient once out, and no role waits on global
+ * memory.  Two forms, chosen per geometry (hipe_cluster_plan reports which):
+ *   resident  the volume stays in the cluster's shared memory between the reduction and the gradient
+ *             write, the L2 holds nothing (bf16 64^3 on 4 CTAs, fp32 56^3 on 6, 32^3 on 1, ...);
+ *   streamed  two rings per CTA: the reduce team's is fed from HBM, the write team's re-reads the same
+ *             stages through L2 at most `lead` stages later, the lead sized so that what has been read
+ *             once and not yet twice stays inside ~40 MB (fp32 64^3 on 8 CTAs; volumes no cluster can
+ *             hold: fp32 96^3 on 16 CTAs, the one non-portable cluster size used).
  *   workspace_dev : >= hipe_cluster_workspace_bytes(...) (256) bytes, 256-byte aligned
- * Returns HIPE_E_UNSUPPORTED otherwise (hipe_cluster_workspace_bytes returns 0 in exactly those
- * cases); hipe_cluster_plan reports the cluster size, ring slots per CTA, stages per CTA share and
- * bytes per stage the launch would use.
+ * Returns HIPE_E_UNSUPPORTED when the geometry cannot be tiled (hipe_cluster_workspace_bytes returns 0
+ * in exactly those cases); hipe_cluster_plan reports the cluster size, ring slots per CTA, stages
+ * per CTA share, bytes per stage, and the lead in stages (0 = resident form).
  */
 HIPE_API long long hipe_cluster_workspace_bytes(int dtype, long long n_vol, int D, int H, int W);
 HIPE_API int hipe_cluster_plan(int dtype, long long n_vol, int D, int H, int W, int* cluster, int* nslots,
-                      int* share_stages, int* stage_bytes);
+                      int* share_stages, int* stage_bytes, int* lead_stages);
 HIPE_API int hipe_joint_loss_cluster(const void* logits_dev, int dtype, long long n_vol, int D, int H, int W,
                             const void* gt_dev, const void* vis_dev, int tgt_dtype, double norm,
                             float* coords_dev, double* expect_dev, float* stats_dev,

@@ -36,7 +36,7 @@ def timeit(fn, bufs, reps=30, warm=5):
     return ts[len(ts) // 2], ts[0]
 
 
-def case(dt, D, B, envs):
+def case(dt, D, B, envs, baselines=True):
     n_vol = B * J
     esz = 4 if dt == torch.float32 else 2
     nbuf = max(3, int(400e6 // (n_vol * D ** 3 * esz)) + 1)
@@ -61,9 +61,10 @@ def case(dt, D, B, envs):
 
     print("%s %d^3 x %d volumes (B=%d)" % ("fp32" if esz == 4 else "bf16", D, n_vol, B), flush=True)
     loss = torch.empty((), dtype=torch.float64, device="cuda")
-    if ops.resident_supported(bufs[0], n_vol, D, D, D) and n_vol >= 296:
+    if baselines and ops.resident_supported(bufs[0], n_vol, D, D, D) and n_vol >= 296:
         rec("resident", lambda x: ops.joint_loss_resident(x, n_vol, D, D, D, gt, vis, 1.0 / B, loss_out=loss))
-    rec("stream fused", lambda x: ops.joint_loss_fused(x, n_vol, D, D, D, gt, vis, 1.0 / B, mode="stream"))
+    if baselines:
+        rec("stream fused", lambda x: ops.joint_loss_fused(x, n_vol, D, D, D, gt, vis, 1.0 / B, mode="stream"))
     for env in envs:
         os.environ.update(env)
         try:
@@ -81,13 +82,67 @@ def case(dt, D, B, envs):
         c, e, s = ops.softargmax_forward(x, n_vol, D, D, D)
         _, gg = ops.l1_loss(c.view(B, 3 * J), gt, vis, 1.0 / B)
         ops.softargmax_backward(x, n_vol, D, D, D, s, e, gg.view(-1, 3))
-    rec("pair fwd+l1+bwd (3V bytes: x1.5)", pair)
+    if baselines:
+        rec("pair fwd+l1+bwd (3V bytes: x1.5)", pair)
     return out
+
+
+def cross_check(dt, D, B, env=None):
+    """cluster launch against the stream launch on the same input (a smoke check before timing;
+    the parity tests proper compare with the oracle)"""
+    os.environ.update(env or {})
+    try:
+        n_vol = B * J
+        g = torch.Generator(device="cuda").manual_seed(7)
+        x = (torch.randn(B, J * D, D, D, generator=g, device="cuda") * 2).to(dt)
+        gt = torch.rand(B, 3 * J, generator=g, device="cuda", dtype=torch.float64) - 0.5
+        vis = (torch.rand(B, 3 * J, generator=g, device="cuda", dtype=torch.float64) > 0.2).double()
+        la, lb = (torch.zeros((), dtype=torch.float64, device="cuda") for _ in range(2))
+        a = ops.joint_loss_cluster(x, n_vol, D, D, D, gt, vis, 1.0 / B, loss_out=la)
+        b = ops.joint_loss_fused(x, n_vol, D, D, D, gt, vis, 1.0 / B, mode="stream", loss_out=lb)
+        torch.cuda.synchronize()
+        names = ("coords", "expect", "stats", "terms", "dlogits")
+        d = {n: float((u.double() - v.double()).abs().max()) for n, u, v in zip(names, a, b)}
+        d["dlogits_rel_to_max"] = d["dlogits"] / float(b[4].double().abs().max())
+        d["loss"] = abs(float(la) - float(lb))
+        print("cross-check %s %d^3 B=%d %s plan=%s: %s" % (dt, D, B, env, ops.cluster_plan(x, n_vol, D, D, D), d), flush=True)
+    finally:
+        for k in (env or {}):
+            del os.environ[k]
 
 
 if __name__ == "__main__":
     quick = "quick" in sys.argv
     f32, bf = torch.float32, torch.bfloat16
+    if "peek" in sys.argv:
+        S8 = {"HIPE_CLUSTER_STREAM": "1", "HIPE_CLUSTER_C": "8"}
+        case(f32, 96, 32, [{}, {}], False)
+        case(f32, 64, 64, [S8, {}, S8, {}], False)
+        sys.exit(0)
+    if "str" in sys.argv:
+        # streamed shares (two rings, second read through L2) against the shared-memory-resident default
+        S, C, L, R = "HIPE_CLUSTER_STREAM", "HIPE_CLUSTER_C", "HIPE_CLUSTER_LEAD", "HIPE_CLUSTER_RSLOTS"
+        st = lambda c, l=None, r=None: dict({S: "1", C: str(c)}, **({L: str(l)} if l else {}), **({R: str(r)} if r else {}))
+        case(f32, 64, 64, [{}, st(8), st(8, 15), st(8, 18), st(8, 24), st(8, 21, 6), st(8, 21, 9), st(8, 18, 6), st(6, 17), st(6, 20), {}], False)
+        case(bf, 64, 128, [{}, st(8), st(8, 12), st(8, 21), st(6), st(6, 14), st(4, 15), st(4, 19), st(4, 19, 6), {}], False)
+        case(bf, 64, 512, [{}, st(8), st(4, 17), {}], False)
+        case(f32, 56, 32, [{}, st(8), st(8, 14), st(8, 26), st(6, 20), {}], False)
+        case(f32, 32, 256, [{}, st(1, 14), st(1, 18), st(1, 12, 7), st(2, 12), {}], False)
+        case(f32, 64, 32, [{}, st(8), st(8, 18), {}], False)
+        sys.exit(0)
+    if "96" in sys.argv:
+        cross_check(f32, 96, 4)
+        cross_check(f32, 96, 3, {"HIPE_CLUSTER_C": "6"})
+        cross_check(f32, 64, 4, {"HIPE_CLUSTER_STREAM": "1"})
+        cross_check(bf, 64, 4, {"HIPE_CLUSTER_STREAM": "1"})
+        cross_check(f32, 80, 2, {})
+        R, L, P, C = "HIPE_CLUSTER_RSLOTS", "HIPE_CLUSTER_LEAD", "HIPE_CLUSTER_POL1", "HIPE_CLUSTER_C"
+        case(f32, 96, 32, [{}, {L: "20"}, {L: "22"}, {L: "25"}, {L: "28"}, {L: "36"}, {L: "25", R: "8"}, {L: "25", R: "12"}, {L: "28", P: "0"},
+                           {C: "8", L: "40"}, {}])
+        case(f32, 96, 64, [{}, {L: "25"}])
+        S8 = {"HIPE_CLUSTER_STREAM": "1", C: "8"}
+        case(f32, 64, 64, [{}, S8, {}, S8, {}, S8], False)
+        sys.exit(0)
     if "56" in sys.argv:
         case(f32, 56, 32, [{}, {"HIPE_CLUSTER_GENERIC": "1"}, {"HIPE_CLUSTER_C": "4"}, {"HIPE_CLUSTER_C": "5"}, {"HIPE_CLUSTER_C": "8"}])
         case(f32, 56, 96, [{}, {"HIPE_CLUSTER_GENERIC": "1"}, {"HIPE_CLUSTER_C": "4"}, {"HIPE_CLUSTER_C": "5"}, {"HIPE_CLUSTER_C": "8"}])

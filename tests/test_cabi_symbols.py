@@ -82,7 +82,9 @@ def test_launch_plan_host_logic():
     assert plan(torch.float32, 1344, 64) == "cluster"       # specialised loops: 4096-byte visits, H | SR
     assert plan(torch.float32, 42, 64) == "cluster"
     assert plan(torch.float32, 2016, 56) == "cluster"       # 3136-byte visits
-    assert plan(torch.float32, 672, 96) == "stream"         # 3.5 MB: does not fit a cluster
+    assert plan(torch.float32, 672, 96) == "cluster"        # 3.5 MB: fits no cluster, streamed shares on 16 CTAs
+    assert plan(torch.float32, 672, 128) == "stream"        # 8 MB: the L2 could not hold one volume per cluster
+    assert plan(torch.bfloat16, 672, 96) == "stream"
     assert plan(torch.float32, 2016, 48) == "stream"        # fits, but the general loops lose to the stream launch
     assert plan(torch.float32, 1344, 32) == "cluster"       # 128 KB volumes
     assert plan(torch.float32, 1344, 16) is None            # 16 KB volumes: forward + recompute backward
@@ -92,10 +94,12 @@ def test_launch_plan_host_logic():
     assert plan(torch.bfloat16, 2688, 16) is None
     assert plan(torch.float64, 1344, 64) is None
     # the plan query behind "cluster": cluster size, ring slots, stages per share, bytes per stage
-    assert ops.cluster_plan(torch.empty(0), 1344, 64, 64, 64) == (6, 14, 11, 16384)
-    assert ops.cluster_plan(torch.empty(0, dtype=torch.bfloat16), 1344, 64, 64, 64) == (4, 14, 8, 16384)
-    assert ops.cluster_plan(torch.empty(0), 672, 56, 56, 56)[3] == 12544
-    assert ops.cluster_plan(torch.empty(0), 672, 96, 96, 96) is None
+    # (cluster, slots, share, stage bytes, lead): fp32 64^3 streams its shares on 8 CTAs, bf16 64^3 and
+    # fp32 56^3 stay resident, fp32 96^3 (fits no cluster) streams wrapped 12 KiB stages on 16 CTAs
+    assert ops.cluster_plan(torch.empty(0), 1344, 64, 64, 64) == (8, 14, 8, 16384, 21)
+    assert ops.cluster_plan(torch.empty(0, dtype=torch.bfloat16), 1344, 64, 64, 64) == (4, 14, 8, 16384, 0)
+    assert ops.cluster_plan(torch.empty(0), 672, 56, 56, 56)[3:] == (12544, 0)
+    assert ops.cluster_plan(torch.empty(0), 672, 96, 96, 96) == (16, 18, 18, 12288, 31)
     # the tiling query behind "resident": supported geometries report a workspace size, others 0
     lib = __import__("hipe_b200._lib", fromlist=["load"]).load()
     assert lib.hipe_resident_workspace_bytes(0, 1344, 64, 64, 64) > 0

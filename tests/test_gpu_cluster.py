@@ -1,6 +1,7 @@
-"""GPU parity of the cluster-resident single launch (hipe_joint_loss_cluster: every volume held in
-the distributed shared memory of one thread-block cluster between the reduction and the gradient
-write) against the fp64 oracle.  Same gates as tests/test_gpu_parity.py."""
+"""GPU parity of the cluster single launch (hipe_joint_loss_cluster) against the fp64 oracle, in both
+of its forms: every volume held in the distributed shared memory of one thread-block cluster
+between the reduction and the gradient write, or streamed shares (two rings per CTA, the second
+read through L2 a bounded lead behind the first).  Same gates as tests/test_gpu_parity.py."""
 import os
 
 import numpy as np
@@ -17,13 +18,16 @@ pytestmark = pytest.mark.gpu
 CLU_GEOMS = [
     (16, 16, 16),
     (32, 32, 32),
-    (64, 64, 64),        # headline: 1 MiB over 6 CTAs x <= 11 stages
+    (64, 64, 64),        # headline: 1 MiB, streamed shares on 8 CTAs (lead 21 stages)
+    (96, 96, 96),        # BASELINE configs[3]: fits no cluster; wrapped 12 KiB stages, streamed on 16 CTAs
+    (32, 96, 96),        # same rows, but fits a cluster: whole-row visits, 192 of 256 team threads
+    (80, 80, 80),        # fits no cluster either, general loops: streamed on 8 CTAs
     (56, 56, 56),        # reference default (main/config.py:23-25): 12.25 KB stages
     (48, 48, 48),
     (16, 128, 64),       # stage = half a z-slice (SR | H, non-zero y base: general row terms)
     (12, 20, 24),        # 30 rows per visit, 180 of 256 team threads active
 ]
-UNSUPPORTED = [(96, 96, 96), (8, 8, 8), (5, 6, 7), (3, 9, 100)]
+UNSUPPORTED = [(8, 8, 8), (5, 6, 7), (3, 9, 100)]
 
 
 @pytest.mark.parametrize("regime", ["noise", "peaked", "sharp"])
@@ -36,7 +40,9 @@ def test_cluster_vs_oracle(geom, regime):
     gt, vis = synth.targets(B, J, seed=11, zero_vis_frac=0.1)
     x = _cuda(hm)
     plan = ops.cluster_plan(x, B * J, D, H, W)
-    assert plan is not None and 1 <= plan[0] <= 8 and plan[2] + 3 <= plan[1], plan
+    assert plan is not None and 1 <= plan[0] <= 16, plan
+    # resident form: the share fits the ring with look-ahead; streamed form: the lead exceeds the share
+    assert (plan[4] == 0 and plan[2] + 3 <= plan[1]) or plan[4] > plan[2], plan
     out = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
     torch.cuda.synchronize()
     worst = _check(hm, gt, vis, D, H, W, B, J, out)
@@ -109,6 +115,89 @@ def test_many_volumes_per_cluster_and_reproducible(monkeypatch):
         else:
             assert torch.equal(out[0], out3[0]) and torch.equal(out[3], out3[3]), env
             assert torch.equal(out[4], out3[4]), (env, (out[4] - out3[4]).abs().max().item())
+
+
+STREAM_CASES = [
+    # (dtype, geometry, env): the streamed form forced onto geometries that default to the resident one,
+    # the resident form forced onto the headline, odd cluster sizes, tiny rings, leads of share + 1
+    ("f32", (64, 64, 64), {"HIPE_CLUSTER_STREAM": "0"}),
+    ("f32", (64, 64, 64), {"HIPE_CLUSTER_STREAM": "1", "HIPE_CLUSTER_C": "5"}),
+    ("f32", (64, 64, 64), {"HIPE_CLUSTER_STREAM": "1", "HIPE_CLUSTER_C": "1", "HIPE_CLUSTER_LEAD": "65"}),
+    ("f32", (64, 64, 64), {"HIPE_CLUSTER_LEAD": "9", "HIPE_CLUSTER_RSLOTS": "2"}),
+    ("f32", (64, 64, 64), {"HIPE_CLUSTER_SLOTS": "6", "HIPE_CLUSTER_RSLOTS": "4"}),
+    ("bf16", (64, 64, 64), {"HIPE_CLUSTER_STREAM": "1"}),
+    ("bf16", (32, 32, 32), {"HIPE_CLUSTER_STREAM": "1", "HIPE_CLUSTER_C": "2"}),
+    ("f32", (56, 56, 56), {"HIPE_CLUSTER_STREAM": "1"}),
+    ("f32", (32, 32, 32), {"HIPE_CLUSTER_STREAM": "1", "HIPE_CLUSTER_C": "3"}),
+    ("f32", (12, 20, 24), {"HIPE_CLUSTER_STREAM": "1"}),
+    ("f32", (96, 96, 96), {"HIPE_CLUSTER_C": "8"}),
+    ("f32", (96, 96, 96), {"HIPE_CLUSTER_C": "7", "HIPE_CLUSTER_LEAD": "43"}),
+    ("f32", (96, 96, 96), {"HIPE_CLUSTER_GENERIC": "1"}),
+    ("bf16", (96, 96, 96), {}),
+]
+
+
+@pytest.mark.parametrize("dt,geom,env", STREAM_CASES, ids=["%s-%s-%s" % (c[0], "x".join(map(str, c[1])), ",".join(
+    "%s=%s" % (k[13:], v) for k, v in c[2].items()) or "default") for c in STREAM_CASES])
+def test_streamed_and_forced_forms_vs_oracle(dt, geom, env, monkeypatch):
+    from hipe_b200 import ops
+    from tests import parity
+    D, H, W = geom
+    J, B = 21, 2
+    hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=23)
+    gt, vis = synth.targets(B, J, seed=23, zero_vis_frac=0.1)
+    x = _cuda(hm)
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    if dt == "bf16":
+        x = x.to(torch.bfloat16)
+        hm = x.float().cpu().numpy().astype(np.float64)
+    plan = ops.cluster_plan(x, B * J, D, H, W)
+    assert plan is not None
+    assert (plan[4] > 0) == (env.get("HIPE_CLUSTER_STREAM") != "0" and (env.get("HIPE_CLUSTER_STREAM") == "1" or geom in (
+        (64, 64, 64), (96, 96, 96)) and not (dt == "bf16" and geom == (64, 64, 64)))), plan
+    out = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+    torch.cuda.synchronize()
+    if dt == "bf16":
+        coords, expect, stats, terms, d = out
+        parity.check_volumes(hm.reshape(B * J, D, H, W), gt.reshape(B * J, 3), vis.reshape(B * J, 3), 1.0 / B,
+                             coords.cpu().numpy(), terms.view(B * J, 3).cpu().numpy(),
+                             d.float().cpu().numpy().reshape(B * J, -1), bf16=True)
+    else:
+        _check(hm, gt, vis, D, H, W, B, J, out)
+
+
+@pytest.mark.parametrize("D", [64, 96])
+def test_streamed_many_volumes_reproducible(D):
+    """The streamed form over more volumes than clusters (both rings lap many times, the lead throttle
+    and the second producer's hand-over are exercised on every volume), bit-reproducible, and the
+    same bits whatever the ring split, the lead or the grid (they change timing, not arithmetic)."""
+    from hipe_b200 import ops
+    H = W = D
+    J, B = 21, 7 if D == 64 else 4        # 147 / 84 volumes over 15 / 7 clusters
+    hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=29)
+    gt, vis = synth.targets(B, J, seed=29, zero_vis_frac=0.1)
+    x = _cuda(hm)
+    loss = torch.full((), float("nan"), dtype=torch.float64, device="cuda")
+    plan = ops.cluster_plan(x, B * J, D, H, W)
+    assert plan[4] > plan[2]
+    out = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B, loss_out=loss)
+    torch.cuda.synchronize()
+    _check(hm, gt, vis, D, H, W, B, J, out)
+    ref = ops.sum_f64(out[3], 1.0 / B)
+    assert abs(loss.item() - ref.item()) <= 1e-14 * abs(ref.item())
+    for env in ({}, {"HIPE_CLUSTER_RSLOTS": "3"}, {"HIPE_CLUSTER_LEAD": str(plan[2] + 1)}, {"HIPE_CLUSTER_LEAD": "200"},
+                {"HIPE_CLUSTER_GRID": "1"}, {"HIPE_CLUSTER_GRID": "2"}, {"HIPE_CLUSTER_SLOTS": "7"}, {"HIPE_CLUSTER_POL1": "0"},
+                {"HIPE_CLUSTER_STASYNC": "0"}):
+        os.environ.update(env)
+        try:
+            out3 = ops.joint_loss_cluster(x, B * J, D, H, W, _cuda(gt), _cuda(vis), 1.0 / B)
+            torch.cuda.synchronize()
+        finally:
+            for k_ in env:
+                del os.environ[k_]
+        assert torch.equal(out[0], out3[0]) and torch.equal(out[3], out3[3]), env
+        assert torch.equal(out[4], out3[4]), (env, (out[4] - out3[4]).abs().max().item())
 
 
 def test_cluster_agrees_with_two_launch_path():

@@ -180,7 +180,8 @@ def test_default_module_picks_the_measured_fastest_launch():
     x48 = torch.empty((2, 21 * 48, 48, 48), device="cuda")
     assert ops.fused_plan(x48, 42, 48, 48, 48) == "stream"
     x96 = torch.empty((1, 21 * 96, 96, 96), device="cuda")
-    assert ops.fused_plan(x96, 21, 96, 96, 96) == "stream"
+    assert ops.fused_plan(x96, 21, 96, 96, 96) == "cluster"      # streamed shares on 16 CTAs
+    assert ops.fused_plan(x96.bfloat16(), 21, 96, 96, 96) == "stream"
     x16 = torch.empty((2, 21 * 16, 16, 16), device="cuda")
     assert ops.fused_plan(x16, 42, 16, 16, 16) is None
     hm = synth.heatmaps(16, 21, 64, 64, 64, "peaked", seed=11)
