@@ -16,6 +16,11 @@ cap() {  # name, kernel regex, prof_one args...
 cap cluster_f32_64_B64 k_cluster --op cluster --dtype f32 --B 64
 cap cluster_bf16_64_B512 k_cluster --op cluster --dtype bf16 --B 512
 cap cluster_f32_56_B32 k_cluster --op cluster --dtype f32 --dim 56 --B 32
+cap cluster_f32_96_B32 k_cluster --op cluster --dtype f32 --dim 96 --B 32
+# the resident form of the headline shape (the default before the streamed form), for comparison
+export HIPE_CLUSTER_STREAM=0
+cap clusterres_f32_64_B64 k_cluster --op cluster --dtype f32 --B 64
+unset HIPE_CLUSTER_STREAM
 cap fused_f32_96_B32 k_stream --op fused --dtype f32 --dim 96 --B 32
 cap fwd_f32_64_B32 k_stream --op fwd --dtype f32 --B 32
 ls -la gpurun_out/${tag}_*.ncu-rep

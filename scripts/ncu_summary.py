@@ -60,6 +60,8 @@ CAPTURES = [("%s_resident_f32" % tag, "resident", "f32_64_B64"),
             ("%s_cluster_f32_64_B64" % tag, "cluster", "f32_64_B64"),
             ("%s_cluster_bf16_64_B512" % tag, "cluster", "bf16_64_B512"),
             ("%s_cluster_f32_56_B32" % tag, "cluster", "f32_56_B32"),
+            ("%s_cluster_f32_96_B32" % tag, "cluster", "f32_96_B32"),
+            ("%s_clusterres_f32_64_B64" % tag, "cluster_resident_form", "f32_64_B64"),
             ("%s_fused_f32_96_B32" % tag, "fused", "f32_96_B32"),
             ("%s_fwd_f32_64_B32" % tag, "softargmax_fwd", "f32_64_B32")]
 for name, key, cfgkey in CAPTURES:
