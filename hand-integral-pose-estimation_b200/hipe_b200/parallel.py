@@ -16,12 +16,14 @@ gradient by 1/world, exactly what `Reduce.backward` broadcasts (balanced_paralle
 
 How the record travels:
   * equal shards known a priori on CUDA (the training loop): NVLink peer memory, no NCCL launch --
-    `hipe_peer_publish` on the stream of the loss kernels (stores + flag, never waits) and
-    `hipe_peer_collect` on a side stream (waits for the peers, combines).  The main stream meets the
-    collect of step t only before the publish of step t+1, or when the loss value / the gathered
-    joints are consumed (the returned loss is a `DeferredLoss`: any use of its value first makes
-    the current stream wait for the collect), so a slow rank or a host hiccup costs the others
-    nothing until a full step later.  `defer=False` keeps the one-kernel form
+    `hipe_peer_publish` (stores + flag, never waits) and `hipe_peer_collect` (waits for the peers,
+    combines) both on a side stream that waits for the step's loss kernel; they run on the SMs the
+    persistent loss launch of the next step leaves idle.  The stream of the loss kernels only
+    records an event per step and waits for the collect of step t-2 (which bounds the lifetime of
+    the buffers the side stream touches), or for the collect of step t when the loss value / the
+    gathered joints are consumed (the returned loss is a `DeferredLoss`: any use of its value first
+    makes the current stream wait), so a slow rank or a host hiccup costs the others nothing until
+    two steps later.  `HIPE_PUBLISH_STREAM=main` keeps the publish in stream order.  `defer=False` keeps the one-kernel form
     (`hipe_peer_exchange`) in stream order.
   * anything else (unequal / unknown shard sizes, CPU / gloo, no symmetric memory): one
     `all_gather` of the record.
@@ -218,6 +220,10 @@ class _PeerExchange:
         self.ev_pub = [torch.cuda.Event() for _ in range(4)]
         self.ev_col = [torch.cuda.Event() for _ in range(4)]
         self.last_col = None
+        # HIPE_PUBLISH_STREAM=main keeps the publish in stream order behind the loss kernels (18 us per
+        # step on their stream); default: on the side stream with the collect
+        import os
+        self.publish_on_side = os.environ.get("HIPE_PUBLISH_STREAM", "side") != "main"
         torch.cuda.synchronize(device)
         dist.barrier(group)                    # every buffer is zeroed before anyone's first store
 
@@ -252,25 +258,47 @@ class _PeerExchange:
         if self.err_np.any():
             self.check()
         main = torch.cuda.current_stream(dev)
-        # flow control (see hipe_exchange.cu): publish(t) only after this rank's collect(t-1)
-        if self.last_col is not None:
-            main.wait_event(self.last_col)
         self.seq += 1
         i = self.seq & 3
         ev_pub, ev_col, side = self.ev_pub[i], self.ev_col[i], self.side
-        with ops._launch("peer_publish", coords):
-            _lib.check(lib.hipe_peer_publish(
-                loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
-                self.peers_dev, self.world, self.rank, self.seq, main.cuda_stream))
-        ev_pub.record(main)
+        timed = ops.KERNEL_EVENTS is not None
         value = into.detach() if into is not None else torch.empty((), dtype=torch.float64, device=dev)
         call = self.call_ring[i]
-        # the value's storage must outlive the side-stream write even if the caller drops the loss at
-        # once: at most two collects are outstanding (flow control above), four are kept
-        self.keep[i] = value
-        side.wait_event(ev_pub)
+        if self.publish_on_side:
+            # Publish AND collect on the side stream: the stream of the loss kernels only records an event.
+            # Flow control (see hipe_exchange.cu) -- publish(t) after this rank's collect(t-1) -- is the
+            # side stream's own order.  The loss kernels' stream may run at most two steps ahead of it:
+            # that bounds the lifetime of what the side stream reads and writes (kept for four steps).
+            if self.seq > 2:
+                main.wait_event(self.ev_col[(self.seq - 2) & 3])
+            ev_pub.record(main)
+            side.wait_event(ev_pub)
+            self.keep[i] = (value, loss_scalar, coords)
+            ops.LAUNCHES += 1
+            if timed:
+                p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                p0.record(side)
+            _lib.check(lib.hipe_peer_publish(
+                loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
+                self.peers_dev, self.world, self.rank, self.seq, side.cuda_stream))
+            if timed:
+                p1.record(side)
+                ops.KERNEL_EVENTS.setdefault("peer_publish", []).append((p0, p1))
+        else:
+            # publish in stream order behind the loss kernels (HIPE_PUBLISH_STREAM=main); flow control:
+            # publish(t) only after this rank's collect(t-1)
+            if self.last_col is not None:
+                main.wait_event(self.last_col)
+            with ops._launch("peer_publish", coords):
+                _lib.check(lib.hipe_peer_publish(
+                    loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
+                    self.peers_dev, self.world, self.rank, self.seq, main.cuda_stream))
+            ev_pub.record(main)
+            # the value's storage must outlive the side-stream write even if the caller drops the loss at
+            # once: at most two collects are outstanding (flow control above), four are kept
+            self.keep[i] = value
+            side.wait_event(ev_pub)
         ops.LAUNCHES += 1
-        timed = ops.KERNEL_EVENTS is not None
         if timed:
             t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             t0.record(side)

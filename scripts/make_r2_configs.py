@@ -85,8 +85,13 @@ def main():
     out.append("\n## 2. Same-box A/B of the single-launch kernels (`scripts/ab_cluster.py`)\n")
     out.append("Median of 5 blocks of 30 launches, rotating inputs larger than L2; GB/s and frac on `V*s + V*g` (the pair moves "
                "1.5x that).  `cluster <env>`: `HIPE_CLUSTER_*` overrides; the first `cluster` line of a block is the library's "
-               "own choice.  Final code:\n\n```\n" + (text("r2_ab_cluster_full.log") or "") + "```\n")
-    for name, what in (("r2_ab_cluster_56.log", "56^3 right after its specialisation (3136-byte visits), `scripts/ab_cluster.py 56`"),
+               "own choice.  The build before the streamed form (every `cluster` line is the resident form):\n\n```\n" + (text("r2_ab_cluster_full.log") or "") + "```\n")
+    for name, what in (("r2_ab_cluster_str.log", "Streamed shares forced onto every specialised shape (`scripts/ab_cluster.py str`; `STREAM=1,C=..,LEAD=..,RSLOTS=..` "
+                        "are the overrides, the plain `cluster` lines the resident form that was the default in that build)"),
+                       ("r2_ab_cluster_96c.log", "fp32 96^3: streamed shares on 16-CTA clusters against the stream launch, and the headline shape alternating "
+                        "resident / streamed (`scripts/ab_cluster.py 96`; the cross-check lines compare the two launches' outputs)"),
+                       ("r2_ab_cluster_peek.log", "Early non-blocking barrier peek off / on, two builds alternating (`scripts/ab_cluster_peek.sh`) -- no effect"),
+                       ("r2_ab_cluster_56.log", "56^3 right after its specialisation (3136-byte visits), `scripts/ab_cluster.py 56`"),
                        ("r2_ab_cluster_sym.log", "Symmetric teams (`-DHIPE_CLU_EXPERIMENTS`, `HIPE_CLUSTER_SYM`), `scripts/ab_cluster.py sym` -- negative"),
                        ("r2_ab_cluster_wt2.log", "One reduce team + two write teams (`HIPE_CLUSTER_WT2`), `scripts/ab_cluster.py wt2` -- negative; "
                         "the plain `cluster` lines are the first run after the polynomial / store-hint branches left the loop")):
