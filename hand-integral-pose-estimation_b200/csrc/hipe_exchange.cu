@@ -22,7 +22,11 @@
 
 namespace hipe {
 
-constexpr int kXT = 512;
+constexpr int kXT = 512;       // threads per CTA of the one-kernel form
+// The split form's two launches run beside the next step's persistent loss launch (608 threads x 96
+// registers per SM): with 128 threads x 32 registers their CTAs fit on an SM that already holds one
+// of its CTAs, so a collect that is still polling for a slow rank never keeps a cluster from launching.
+constexpr int kXTSplit = 128;
 constexpr int kXMaxWorld = 64;
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
@@ -68,16 +72,31 @@ __global__ void __launch_bounds__(kXT)
     __shared__ double my_sum_sh;
     __shared__ unsigned my_ticket;
     const int p = blockIdx.x;                 // the peer this CTA serves / the rank it listens to
+    const int nthr = (int)blockDim.x;         // kXT or kXTSplit
     const int par = (int)(seq & 1ull);
     const long long n = B * K;
     // 0. this rank's loss sum, in a fixed order (thread-strided partials -> warp shuffles ->
     //    kXT/32 warp partials); every CTA forms the same bits
     if (threadIdx.x == 0) timed_out = 0;
     if constexpr (kPhase != 2) {
-        double acc = 0.0;
-        for (long long i = threadIdx.x; i < n_in; i += kXT) acc += loss_in[i];
-        acc = warp_sum(acc);
-        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+        // kXT virtual lanes whatever the CTA's size (kXT or kXTSplit threads): thread t accumulates lanes
+        // t, t + nthr, ...; each group of 32 consecutive lanes is one shuffle tree, as in the kXT-thread
+        // launch -- the one-kernel form and the split form give the same bits
+        const int per = kXT / nthr;
+        double acc[kXT / kXTSplit];
+#pragma unroll
+        for (int j = 0; j < kXT / kXTSplit; ++j) {
+            acc[j] = 0.0;
+            if (j < per)
+                for (long long i = threadIdx.x + (long long)j * nthr; i < n_in; i += kXT) acc[j] += loss_in[i];
+        }
+#pragma unroll
+        for (int j = 0; j < kXT / kXTSplit; ++j) {
+            if (j < per) {
+                const double w = warp_sum(acc[j]);
+                if ((threadIdx.x & 31) == 0) red[(threadIdx.x + j * nthr) >> 5] = w;
+            }
+        }
         __syncthreads();
         if (threadIdx.x < 32) {
             double r = warp_sum((threadIdx.x < kXT / 32) ? red[threadIdx.x] : 0.0);
@@ -90,7 +109,7 @@ __global__ void __launch_bounds__(kXT)
         double* dst = peers[p] + ((long long)par * world + rank) * reclen;
         if (threadIdx.x == 0) *reinterpret_cast<double2*>(dst) = make_double2(my_sum_sh, (double)B);
         const long long npair = n >> 1;
-        for (long long i = threadIdx.x; i < npair; i += kXT)
+        for (long long i = threadIdx.x; i < npair; i += nthr)
             *reinterpret_cast<double2*>(dst + 2 + 2 * i) = make_double2((double)coords[2 * i], (double)coords[2 * i + 1]);
         if ((n & 1) && threadIdx.x == 0) dst[2 + n - 1] = (double)coords[n - 1];
     }
@@ -123,7 +142,7 @@ __global__ void __launch_bounds__(kXT)
     if (!timed_out) {
         if (coords_all) {
             double* out = coords_all + (long long)p * n;
-            for (long long i = threadIdx.x; i < n; i += kXT) out[i] = ld_relaxed_sys_f64(slot + 2 + i);
+            for (long long i = threadIdx.x; i < n; i += nthr) out[i] = ld_relaxed_sys_f64(slot + 2 + i);
         }
         if (threadIdx.x == 0) scratch[p] = ld_relaxed_sys_f64(slot);
     } else if (threadIdx.x == 0) {
@@ -193,7 +212,7 @@ extern "C" int hipe_peer_publish(const double* loss_in, long long n_in, double i
     if (world <= 0 || world > kXMaxWorld || rank < 0 || rank >= world || B <= 0 || K <= 0 || seq == 0 || n_in <= 0)
         return HIPE_E_SHAPE;
     const long long reclen = hipe_peer_exchange_reclen(B, K);
-    k_peer_exchange<1><<<world, kXT, 0, static_cast<cudaStream_t>(stream)>>>(
+    k_peer_exchange<1><<<world, kXTSplit, 0, static_cast<cudaStream_t>(stream)>>>(
         loss_in, n_in, in_scale, coords, B, K, reinterpret_cast<double* const*>(peers_dev), world, rank, seq, reclen,
         0.0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0ull);
     return (int)cudaGetLastError();
@@ -208,7 +227,7 @@ extern "C" int hipe_peer_collect(void* const* peers_dev, int world, int rank, un
         return HIPE_E_SHAPE;
     const long long reclen = hipe_peer_exchange_reclen(B, K);
     const unsigned long long tns = (unsigned long long)((timeout_s > 0 ? timeout_s : 20.0) * 1e9);
-    k_peer_exchange<2><<<world, kXT, 0, static_cast<cudaStream_t>(stream)>>>(
+    k_peer_exchange<2><<<world, kXTSplit, 0, static_cast<cudaStream_t>(stream)>>>(
         nullptr, 0, 0.0, nullptr, B, K, reinterpret_cast<double* const*>(peers_dev), world, rank, seq, reclen,
         value_scale, value_out, sums_out, coords_all, err, scratch, reinterpret_cast<unsigned*>(scratch + world), tns);
     return (int)cudaGetLastError();
