@@ -365,7 +365,14 @@ def joint_loss_fused(logits, n_vol, D, H, W, gt, vis, norm, cluster=None, varian
     mode = FUSED_MODE if mode is None else mode
     plan = fused_plan(logits, n_vol, D, H, W) if (mode == "auto" and cluster is None and variant is None) else None
     if mode == "cluster" or plan == "cluster":
-        return joint_loss_cluster(logits, n_vol, D, H, W, gt, vis, norm, loss_out, want_aux)
+        try:
+            return joint_loss_cluster(logits, n_vol, D, H, W, gt, vis, norm, loss_out, want_aux)
+        except _lib.HipeError as e:
+            # the plan is made from the geometry alone; a device that cannot co-schedule the cluster shape
+            # (a partition with fewer SMs per GPC than the cluster) answers UNSUPPORTED at launch time:
+            # the streaming launch below takes every geometry
+            if mode == "cluster" or "error %d:" % _lib.E_UNSUPPORTED not in str(e):
+                raise
     if mode == "resident" or plan == "resident":
         try:
             return joint_loss_resident(logits, n_vol, D, H, W, gt, vis, norm, loss_out, want_aux)
