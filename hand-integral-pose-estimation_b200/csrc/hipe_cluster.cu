@@ -1059,6 +1059,10 @@ struct Geom {
 };
 constexpr int kWrapKP = 3;
 constexpr int kStrMargin = 13;   // streamed shares: default lead = share + this many stages
+constexpr int kStrMinMargin = 9;
+// what the 126 MB L2 serves of a read-once / reuse-once stream while the gradient stores pass through it
+// (ncu DRAM read bytes against the lead, profiles/r2_configs.md section 5)
+constexpr double kStrL2Bytes = 42e6;
 
 static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) {
     const int esz = dtype == HIPE_F32 ? 4 : 2;
@@ -1137,24 +1141,46 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
     (void)n_vol;
     // Streamed shares (two rings, second read through L2).  Any cluster size works, nothing is resident;
     // what matters is what the L2 must hold between the two reads: `lead` stages per CTA = one volume
-    // per cluster + kStrMargin stages per CTA.  Measured with ncu (fp32, DRAM read bytes / algorithmic):
-    // 64^3 C=8 (41 MB) 1.03, C=6 (52 MB) 1.21, C=4 (63 MB) 1.42; 96^3 C=8 lead 37 (55 MB) 1.40, the same
-    // on 12 / 9 clusters (47 / 35 MB) 1.14 / 1.01, C=16 lead 31 (43 MB) 1.03: about 40 MB of the 126 MB L2
-    // serve this pattern.  So: 8 CTAs if that fits 44 MB, else 16 (one cluster per GPC, 112 SMs).
-    // Taken when no cluster can hold the volume, and -- because the two rings decouple the teams, which
-    // is worth more than the 12 SMs a cluster of 8 leaves idle -- for 4-byte volumes of the 4096-byte
-    // geometry with shares of >= 8 stages that fit the 44 MB at C = 8 (fp32 64^3 x 1344, same box,
-    // alternating: 0.473-0.495 ms streamed vs 0.500-0.518 resident; x 672: 0.257 vs 0.269).  It loses
-    // where the share is short or the gradient pass is XU-bound (bf16 64^3 x 2688: 0.60 vs 0.54; fp32
-    // 56^3 x 672: 0.190-0.205 vs 0.187-0.192; fp32 32^3 x 5376: 0.264 vs 0.242).
-    // HIPE_CLUSTER_STREAM=1 / 0 forces / forbids it.
-    const long long vol_bytes = NR * row_b;
-    const double mb8 = (15.0 * (double)vol_bytes + 120.0 * kStrMargin * g->stage_bytes) / 1e6;
+    // per cluster + a margin per CTA.  Measured with ncu (fp32, DRAM read bytes / algorithmic): 64^3 C=8
+    // lead 21 (41 MB) 1.03, C=6 lead 24 (52 MB) 1.21, C=4 (63 MB) 1.42; 96^3 C=8 lead 37 (55 MB) 1.40, the
+    // same on 12 / 9 clusters (47 / 35 MB) 1.14 / 1.01, C=16 lead 31 (43 MB) 1.03: a little over 40 MB of
+    // the 126 MB L2 serve this pattern.
+    // Taken when no cluster can hold the volume, and -- because the two rings decouple the teams -- for
+    // 4-byte volumes of the 4096-byte geometry with >= 64 stages for which some cluster size fits that
+    // bound (fp32 64^3 x 1344, same box, alternating: 0.473-0.495 ms streamed at C=8 vs 0.500-0.518
+    // resident; x 672: 0.257 vs 0.269).  It loses where the share is short or the gradient pass is
+    // XU-bound (bf16 64^3 x 2688: 0.60 vs 0.54; fp32 56^3 x 672: 0.190-0.205 vs 0.187-0.192; fp32 32^3 x
+    // 5376: 0.264 vs 0.242).  HIPE_CLUSTER_STREAM=1 / 0 forces / forbids it.
+    // The cluster size of the streamed form: what has been read once and not yet twice is
+    // lead x stage bytes x CTAs, and it must stay inside kStrL2Bytes.  Among the sizes that leave a
+    // margin (lead - share) of >= kStrMinMargin stages for the cross-CTA merge and the HBM latency, the
+    // one that keeps the most SMs busy (ties: the larger margin); lead = share + kStrMargin, capped by
+    // the L2 bound.  fp32 64^3: C=8, lead 21 (120 SMs, 41 MB); fp32 96^3: C=16, lead 30 (112 SMs, 41 MB).
+    // The bound is sharp and it pays to stay clear of it: C=6 at lead 20 (132 SMs, 43.3 MB) wins a
+    // back-to-back loop of launches on a warm box (scripts/ab_cluster.py lead lead2: 0.468-0.472 ms vs
+    // 0.50-0.53) but loses the training step, where other kernels run between the launches (bench.py,
+    // alternating processes: 0.507-0.509 vs 0.468-0.473 ms per step), and at lead 22 loses both.
+    // No size fits (fp32 128^3): C = 8 with the plain lead; the second read then misses L2 in part, like
+    // the streaming launch's.
+    const int maxC = g->wrap ? kMaxClusterStr : kMaxCluster;     // (16-CTA exchange buffers: wrapped kernel only)
+    static const int kSMsStr[kMaxClusterStr + 1] = {0, 148, 148, 135, 132, 130, 132, 105, 120, 0, 0, 0, 0, 0, 0, 0, 112};
+    int bestC = 0, bestLead = 0, bestSMs = 0, bestMargin = 0;
+    for (int C = 1; C <= maxC; ++C) {
+        if (kSMsStr[C] == 0 || g->NSv < C) continue;
+        const int share = (g->NSv + C - 1) / C;
+        const int lead_max = (int)(kStrL2Bytes / ((double)kSMsStr[C] * g->stage_bytes));
+        const int margin = lead_max - share;
+        if (margin < kStrMinMargin) continue;
+        if (kSMsStr[C] > bestSMs || (kSMsStr[C] == bestSMs && margin > bestMargin)) {
+            bestC = C; bestSMs = kSMsStr[C]; bestMargin = margin;
+            bestLead = share + kStrMargin < lead_max ? share + kStrMargin : lead_max;
+        }
+    }
     {
         int force = -1;
         if (const char* env = getenv("HIPE_CLUSTER_STREAM")) force = atoi(env);
         const bool prefer = esz == 4 && g->stage_bytes == kKP * kC * 16 && g->nact == kC && g->SR % H == 0 &&
-                            g->NSv >= 8 * kMaxCluster && mb8 <= 44.0 && !want;
+                            g->NSv >= 8 * kMaxCluster && bestC > 0 && !want;
         if (g->C > 0 && (force == 0 || (force < 0 && !prefer))) return true;
         if (g->C == 0 && force == 0) return false;
     }
@@ -1166,8 +1192,7 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
     }
     if (nslots < 6) return false;
     g->nslots = nslots;
-    const int maxC = g->wrap ? kMaxClusterStr : kMaxCluster;     // (16-CTA exchange buffers: wrapped kernel only)
-    int C = (mb8 <= 44.0) ? kMaxCluster : maxC;
+    int C = bestC > 0 ? bestC : kMaxCluster;
     if (want >= 1 && want <= maxC) C = want;
     while (C > 1 && g->NSv < C) --C;
     g->C = C;
@@ -1178,7 +1203,7 @@ static bool pick_geom(int dtype, long long n_vol, int D, int H, int W, Geom* g) 
         const int v = atoi(env);
         if (v >= 2 && v <= nslots - 2) g->nslots_r = v;
     }
-    g->lead = g->max_share + kStrMargin;
+    g->lead = (C == bestC) ? bestLead : g->max_share + kStrMargin;
     if (const char* env = getenv("HIPE_CLUSTER_LEAD")) {
         const int v = atoi(env);
         if (v > g->max_share) g->lead = v;

@@ -114,6 +114,18 @@ def cross_check(dt, D, B, env=None):
 if __name__ == "__main__":
     quick = "quick" in sys.argv
     f32, bf = torch.float32, torch.bfloat16
+    if "lead" in sys.argv:
+        # streamed form of the headline shape: cluster size x lead (what the L2 must hold) x ring split
+        S, C, L, R = "HIPE_CLUSTER_STREAM", "HIPE_CLUSTER_C", "HIPE_CLUSTER_LEAD", "HIPE_CLUSTER_RSLOTS"
+        st = lambda c, l=None, r=None: dict({S: "1", C: str(c)}, **({L: str(l)} if l else {}), **({R: str(r)} if r else {}))
+        if "lead2" in sys.argv:
+            a6, b6, c6, d6 = st(6, 20, 7), st(6, 22, 7), st(6, 21, 6), st(6, 20, 8)
+            case(f32, 64, 64, [{}, a6, {}, b6, {}, c6, {}, d6, {}, a6, {}, b6, {}, c6, {}, d6, {}], False)
+            case(f32, 64, 32, [{}, a6, {}, b6, {}, a6, {}], False)
+            sys.exit(0)
+        case(f32, 64, 64, [{}, st(8, 20), st(8, 22), st(8, 23), {}, st(6, 18), st(6, 19), st(6, 21), st(6, 22), {}, st(6, 20, 7), st(6, 20, 9),
+                           st(5, 21), st(5, 23), st(8, 21, 7), {}], False)
+        sys.exit(0)
     if "peek" in sys.argv:
         S8 = {"HIPE_CLUSTER_STREAM": "1", "HIPE_CLUSTER_C": "8"}
         case(f32, 96, 32, [{}, {}], False)
