@@ -114,6 +114,7 @@ struct Params {
     int nslots_r;     // streamed shares (kMode 3): slots [0, nslots_r) feed the reduce team, the rest the write team
     int lead;         // streamed shares: stages the first producer may run ahead of the write team (> share)
     int pol1;         // streamed shares: L2 policy of the first read (0 normal, 1 evict_first, 2 evict_last)
+    int pf;           // resident form: stages the producer prefetches into L2 when it blocks on a held slot (0: none)
     // outputs (nullable except out)
     float* coords;
     double* expect;
@@ -319,6 +320,11 @@ __device__ __forceinline__ float2 ex2_poly2(float2 a) {
     q = __ffma2_rn(q, f, make_float2(0.9999992847442627f, 0.9999992847442627f));
     return make_float2(__int_as_float(__float_as_int(q.x) + (__float_as_int(t.x) << 23)),
                        __int_as_float(__float_as_int(q.y) + (__float_as_int(t.y) << 23)));
+}
+
+// bulk prefetch global -> L2 (no shared-memory slot needed): what the producer cannot load yet
+__device__ __forceinline__ void prefetch_l2(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 
 // ring position of a role: slot index and the parity of the slot's current use
@@ -590,10 +596,32 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
                                                       : (p.pol1 == 2 ? policy_evict_last() : policy_evict_normal());
             Ring r;
             r.init();
+            // Resident form: a slot is held until its gradient is written, so the last (share - spare)
+            // stages of the next volume can only be requested once the write team frees slots, and their
+            // HBM latency (2-3.5 us under load) sits in the per-volume loop write(k) -> load -> reduce ->
+            // merge -> write(k+1).  When the producer is about to block on a held slot it therefore first
+            // asks the L2 for the next p.pf stages (bulk prefetch, no slot needed): the late loads take an
+            // L2 hit.
+            long long pk = 0;      // prefetch cursor: volume, stage (never behind the load cursor)
+            int ps = 0;
+            auto prefetch_from = [&](long long k, int s) {     // stages (k, s) .. (k, s) + p.pf - 1, each once
+                if (pk < k || (pk == k && ps < s)) { pk = k; ps = s; }
+                long long tk = k;
+                int ts = s + p.pf;
+                while (ts >= nst) { ts -= nst; ++tk; }
+                while (pk < nv && (pk < tk || (pk == tk && ps < ts))) {
+                    const long long pvol = cluster_id + pk * p.n_clusters;
+                    prefetch_l2(p.in + pvol * p.vol_bytes + (long long)(sv0 + ps) * stage_bytes, (uint32_t)stage_bytes);
+                    if (++ps == nst) { ps = 0; ++pk; }
+                }
+            };
             for (long long k = 0; k < nv; ++k) {
                 const long long vol = cluster_id + k * p.n_clusters;
                 const unsigned char* src = p.in + vol * p.vol_bytes + (long long)sv0 * stage_bytes;
                 for (int s = 0; s < nst; ++s) {
+                    if constexpr (!kStr) {
+                        if (p.pf > 0 && r.lap > 0 && !test_cta(smem_u32(&sm.empty[r.slot]), (r.lap - 1) & 1)) prefetch_from(k, s);
+                    }
                     if constexpr (kStr) {
                         // Streamed shares: stay at most `lead` stages ahead of the write team -- what has
                         // been read once and not yet again is what the L2 must hold (lead x stage bytes x
@@ -993,6 +1021,14 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
     };
 
     // (wcount: stages write warp 0 has taken so far, all volumes)
+    // Also built and dropped (bf16 64^3, resident form): the reduce team leaving its exponentials IN PLACE
+    // of the logits (bf16, relative to a warp-uniform offset kept per slot) so that the write team
+    // scales them instead of exponentiating again -- one MUFU.EX2 per element instead of two.  Parity-
+    // green (one more bf16 rounding, inside the 1-ulp gate) and the gradient write of a volume did drop
+    // from 5.0 to 4.1 us, but the launch did not move (0.531 vs 0.531 ms x 2688; 2.18 vs 2.19-2.20 x
+    // 10752): the period per volume (6.6 us) is the loop write(k) frees 2 slots -> last TMA of volume k+1
+    // -> 2.2-3.4 us until it lands -> last stage + fold 0.8 -> merge incl. the slowest peer 1.8 ->
+    // write(k+1), not the write team's arithmetic.
     // Team roles.  kMode 0 (what ships): team 0 reduces every volume, team 1 writes every volume.
     // Two other layouts were built to relieve the 2-byte gradient pass (the write team is > 90 % busy
     // there) and both lost on every shape; they compile only with -DHIPE_CLU_EXPERIMENTS and are
@@ -1334,6 +1370,12 @@ extern "C" int hipe_joint_loss_cluster(const void* logits, int dtype, long long 
     p.lead = g.lead;
     p.pol1 = 2;
     if (const char* env = getenv("HIPE_CLUSTER_POL1")) p.pol1 = atoi(env);
+    // L2 prefetch of the stages the producer cannot load yet (resident form), where it was measured to pay:
+    // fp32 56^3 x 672 0.179-0.184 vs 0.184-0.195 ms, bf16 32^3 x 5376 0.172-0.175 vs 0.190-0.198; neutral or
+    // slightly negative on bf16 64^3 (0.542-0.561 vs 0.530-0.564 on a drifting box), fp32 32^3 (0.254 vs
+    // 0.243) and the resident form of fp32 64^3.  HIPE_CLUSTER_PF overrides (stages; 0 = off).
+    p.pf = ((dtype == HIPE_F32 && g.pass_bytes == 3136) || (dtype == HIPE_BF16 && g.C == 1 && !g.streamed)) ? 4 : 0;
+    if (const char* env = getenv("HIPE_CLUSTER_PF")) p.pf = atoi(env);
     p.coords = coords; p.expect = expect; p.stats = stats; p.loss_terms = loss_terms;
     p.gt = gt; p.vis = vis; p.tgt_f64 = (tgt_dtype == HIPE_F64); p.norm = norm;
     p.ticket = static_cast<unsigned*>(workspace);
