@@ -31,6 +31,7 @@ extern "C" const char* hipe_strerror(int code) {
         case HIPE_E_CLUSTER: return "cluster size must be 0, 1, 2, 4, 8 or 16";
         case HIPE_E_ARCH: return "current device is not sm_100 (Blackwell B200)";
         case HIPE_E_UNSUPPORTED: return "geometry or launch not supported by this entry point";
+        case HIPE_E_LIMIT: return "size beyond the fixed scratch of this no-alloc entry point (see the limits in hipe_b200.h); use the general entry point";
         default: break;
     }
     if (code > 0) return cudaGetErrorString((cudaError_t)code);

@@ -6,6 +6,7 @@
 // the whole scoring stays on the GPU.  Latency-bound (N*K doubles, 0.67 MB at 3960 x 21): one
 // CTA per keypoint, integer histograms only (bit-deterministic), no roofline claimed.  sm_100a.
 #include "hipe_common.cuh"
+#include <mutex>
 
 namespace hipe {
 
@@ -245,6 +246,62 @@ extern "C" int hipe_keypoint_measures(const double* dist, const unsigned char* v
     if (workspace_bytes < hipe_keypoint_measures_workspace_bytes(K, steps)) return HIPE_E_SHAPE;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     double* cnt = workspace;
+    double* mean = cnt + K;
+    double* med = mean + K;
+    double* auc = med + K;
+    double* pck = auc + K;
+    k_keypoint_measures<<<K, kMT, 0, st>>>(dist, vis, N, K, val_min, val_max, steps, cnt, mean, med, auc, pck);
+    k_measures_final<<<1, 256, 0, st>>>(cnt, mean, med, auc, pck, K, steps, summary, pck_curve);
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// hipe_keypoint_measures_noalloc: the same two launches with the per-keypoint scratch in a
+// file-scope device array instead of caller-owned memory, for callers that must not allocate
+// (CUDA graph capture, serving loops).  No counterpart in the reference.
+// Every GPU that loads the library holds the array until exit.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_measures_scratch[HIPE_NOALLOC_MEASURES_MAX_DOUBLES];
+
+// The array's name is a host-side stand-in in host code, not a device address: the address the
+// kernels get comes from cudaGetSymbolAddress, asked once per device with that device current.
+static int measures_scratch(double** out) {
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static double* ptr[kMaxDev] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kMaxDev) return HIPE_E_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_measures_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!p) return HIPE_E_NULL;
+        ptr[dev] = static_cast<double*>(p);
+    }
+    *out = ptr[dev];
+    return 0;
+}
+
+extern "C" int hipe_keypoint_measures_noalloc(const double* dist, const unsigned char* vis, long long N, int K,
+                                              double val_min, double val_max, int steps, double* summary,
+                                              double* pck_curve, void* stream) {
+    if (!dist || !summary || !pck_curve) return HIPE_E_NULL;
+    if (N < 0 || K <= 0 || steps <= 0 || steps > kMaxSteps) return HIPE_E_SHAPE;
+    if (K > HIPE_NOALLOC_MEASURES_MAX_K ||
+        (long long)K * (4 + (long long)steps) > (long long)HIPE_NOALLOC_MEASURES_MAX_DOUBLES)
+        return HIPE_E_LIMIT;
+    double* ws = nullptr;
+    const int rc = measures_scratch(&ws);
+    if (rc != 0) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // the array keeps the previous call's contents: the part this call uses starts at zero
+    const size_t used = sizeof(double) * ((size_t)K * 4 + (size_t)K * steps);
+    cudaError_t e = cudaMemsetAsync(ws, 0, used, st);
+    if (e != cudaSuccess) return (int)e;
+    double* cnt = ws;
     double* mean = cnt + K;
     double* med = mean + K;
     double* auc = med + K;

@@ -10,6 +10,7 @@ from . import _build
 
 F32, BF16, F64 = 0, 1, 3
 E_UNSUPPORTED = -7
+E_LIMIT = -8
 VARIANT_AUTO, VARIANT_TMA, VARIANT_LDG = 0, 1, 2
 
 _c = ctypes
@@ -43,6 +44,7 @@ SIGNATURES = {
                                         _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "hipe_keypoint_measures_workspace_bytes": (_ll, [_i, _i]),
     "hipe_keypoint_measures": (_i, [_vp, _vp, _ll, _i, _d, _d, _i, _vp, _vp, _vp, _ll, _vp]),
+    "hipe_keypoint_measures_noalloc": (_i, [_vp, _vp, _ll, _i, _d, _d, _i, _vp, _vp, _vp]),
     "hipe_orthonormalize3_fwd": (_i, [_vp, _i, _ll, _vp, _vp, _vp]),
     "hipe_orthonormalize3_bwd": (_i, [_vp, _i, _ll, _vp, _vp, _vp]),
     "hipe_peer_exchange_reclen": (_ll, [_ll, _i]),

@@ -44,6 +44,7 @@ extern "C" {
 #define HIPE_E_CLUSTER (-5)  /* cluster size not in {0,1,2,4,8,16}                    */
 #define HIPE_E_ARCH (-6)     /* current device is not compute capability 10.x         */
 #define HIPE_E_UNSUPPORTED (-7) /* this entry point cannot take the geometry / launch: use the general one */
+#define HIPE_E_LIMIT (-8)    /* size beyond the fixed scratch of a *_noalloc entry point: use the general one */
 
 /* variant selector for the streaming kernels (0 = library default) */
 #define HIPE_VARIANT_AUTO 0
@@ -261,6 +262,28 @@ HIPE_API int hipe_keypoint_measures(const double* dist_dev, const unsigned char*
                            double val_min, double val_max, int steps, double* summary_dev,
                            double* pck_curve_dev, double* workspace_dev, long long workspace_bytes,
                            void* stream);
+
+/*
+ * hipe_keypoint_measures without caller-owned scratch and without any allocation: NO COUNTERPART IN THE
+ * REFERENCE -- added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same two launches,
+ * same results as hipe_keypoint_measures; the per-keypoint scratch is a file-scope __device__ array of
+ * HIPE_NOALLOC_MEASURES_MAX_DOUBLES doubles (514 KiB; every GPU that loads the library holds it until
+ * exit).  Calls neither cudaMalloc / cudaFree nor any allocating library routine (the device address of
+ * the array is asked once per device, on that device's first call, with cudaGetSymbolAddress).
+ *   limits : K <= HIPE_NOALLOC_MEASURES_MAX_K and K * (4 + steps) <= HIPE_NOALLOC_MEASURES_MAX_DOUBLES
+ *            (steps <= 1024 as for the general entry point); beyond them returns HIPE_E_LIMIT
+ *            ("size beyond the fixed scratch ...") and launches nothing.
+ *   All calls on a device share the one array, which keeps the last call's contents (the part a call
+ *   uses is cleared in stream order first): calls that OVERLAP on the GPU -- different streams without
+ *   an event between them -- race on it.  One call at a time per device; use the general entry point
+ *   with separate workspaces for concurrent streams.  The per-keypoint values are not exposed.
+ */
+#define HIPE_NOALLOC_MEASURES_MAX_K 64
+#define HIPE_NOALLOC_MEASURES_MAX_DOUBLES (64 * (4 + 1024))
+HIPE_API int hipe_keypoint_measures_noalloc(const double* dist_dev, const unsigned char* vis_dev, long long N, int K,
+                                   double val_min, double val_max, int steps, double* summary_dev,
+                                   double* pck_curve_dev, void* stream);
 
 /*
  * Batched 3x3 orthonormalisation: replaces make_orthonormal
