@@ -145,8 +145,11 @@ struct SmemT {
     unsigned long long red_ready[kPB], red_free[kPB];      // reduce team <-> merge warp
     unsigned long long scal_ready[kNB], scal_free[kNB];    // merge warp <-> write team
     unsigned long long xfull[2];                           // C remote arrivals per volume
-    unsigned long long rdone[2];                           // streamed shares: reduce team finished volume k
-    unsigned wprog, wprog_pad;                             // streamed shares: stages the write team has taken (warp 0)
+    // Streamed shares, pacing only (no data is ordered by them, so plain counters instead of mbarriers:
+    // a one-directional mbarrier would lose a phase if its producer ever ran two volumes ahead of its
+    // consumer): warps of the reduce team that have finished their volume (kNW per volume), and
+    // stages the write team has taken (warp 0).
+    unsigned rcount, wprog;
     double wred[kPB][kNW][8];
     float wmax[kPB][kNW];
     double xch[2][MC][8];                                  // [buffer][source rank][7 sums + max]
@@ -210,11 +213,14 @@ __device__ long long g_trace[kTraceN][kTraceE];
 #endif
 constexpr uint32_t kSuspendNs = HIPE_CLU_SUSPEND_NS;
 
-// mbarrier waits that trap instead of hanging the GPU if the pipeline logic is ever wrong
+// mbarrier waits that trap instead of hanging the GPU if the pipeline logic is ever wrong.  A failed
+// try_wait costs up to kSuspendNs (20 us), so kSpinLimit of them are ~10 s: four orders of magnitude
+// above any legitimate wait inside a launch that lasts milliseconds, and well inside a test's time-out.
+constexpr unsigned kSpinLimit = 1u << 19;
 __device__ __forceinline__ void wait_cta(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
 #pragma unroll 1
-    for (unsigned spin = 0; spin < (1u << 26); ++spin) {
+    for (unsigned spin = 0; spin < kSpinLimit; ++spin) {
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
@@ -231,7 +237,7 @@ __device__ __forceinline__ void wait_cta(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void wait_cluster(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
 #pragma unroll 1
-    for (unsigned spin = 0; spin < (1u << 26); ++spin) {
+    for (unsigned spin = 0; spin < kSpinLimit; ++spin) {
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
@@ -437,10 +443,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
         // plain-store exchange: one remote arrive per peer
         mbar_init(smem_u32(&sm.xfull[0]), p.stasync ? 1 : C);
         mbar_init(smem_u32(&sm.xfull[1]), p.stasync ? 1 : C);
-#pragma unroll
-        for (int s = 0; s < 2; ++s) {
-            mbar_init(smem_u32(&sm.rdone[s]), kNW);
-        }
+        sm.rcount = 0;
         sm.wprog = 0;
         mbar_fence_init();
         fence_proxy_async();
@@ -456,7 +459,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
     if (kStr && threadIdx.x >= kTeamThreads + 64) {
         // -------------------- second producer warp (streamed shares) --------------------
         // Re-reads the share for the write team, from L2: volume k's stages are requested only after
-        // this CTA's reduce team has consumed them all (rdone), and as far ahead of the write team as
+        // this CTA's reduce team has consumed them all (rcount), and as far ahead of the write team as
         // its ring allows -- the prefetch runs under the cross-CTA merge of the volume.
         if ((threadIdx.x & 31) == 0) {
             const uint64_t pol = policy_evict_first();
@@ -465,7 +468,15 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
             for (long long k = 0; k < nv; ++k) {
                 const long long vol = cluster_id + k * p.n_clusters;
                 const unsigned char* src = p.in + vol * p.vol_bytes + (long long)sv0 * stage_bytes;
-                wait_cta(smem_u32(&sm.rdone[k & 1]), (uint32_t)(k >> 1) & 1);
+                {
+                    // (only so that the re-read finds the lines in L2: the first read of the share is done)
+                    const unsigned need = (unsigned)(k + 1) * (unsigned)kNW;
+                    unsigned spin = 0;
+                    while ((int)(*(volatile unsigned*)&sm.rcount - need) < 0) {
+                        __nanosleep(100);
+                        if (++spin > (1u << 26)) __trap();
+                    }
+                }
                 for (int s = 0; s < nst; ++s) {
                     if (r.lap > 0) wait_cta(smem_u32(&sm.empty[wbase + r.slot]), (r.lap - 1) & 1);
                     const uint32_t bar = smem_u32(&sm.full[wbase + r.slot]);
@@ -793,7 +804,7 @@ __global__ void __maxnreg__(kMode == 2 ? kMaxRegs2 : kMaxRegs) k_cluster(const P
             }
             if constexpr (kStr) {
                 // the whole share has been requested and consumed: the second producer may re-read it
-                if (lane == 0) mbar_arrive(smem_u32(&sm.rdone[k & 1]));
+                if (lane == 0) atomicAdd(&sm.rcount, 1u);
             }
             if (warp == 0) CLU_TRACE(k, 2);
             // ---- fold the thread's accumulators, sum over the warp, hand to the merge warp ----

@@ -186,7 +186,11 @@ def test_streamed_many_volumes_reproducible(D):
     _check(hm, gt, vis, D, H, W, B, J, out)
     ref = ops.sum_f64(out[3], 1.0 / B)
     assert abs(loss.item() - ref.item()) <= 1e-14 * abs(ref.item())
+    # (the last two: a write team starved by a 2-slot ring behind an unthrottled reduce team that runs
+    # volumes ahead -- the pacing counters must not lose a volume)
     for env in ({}, {"HIPE_CLUSTER_RSLOTS": "3"}, {"HIPE_CLUSTER_LEAD": str(plan[2] + 1)}, {"HIPE_CLUSTER_LEAD": "200"},
+                {"HIPE_CLUSTER_LEAD": "100000", "HIPE_CLUSTER_RSLOTS": str(plan[1] - 2), "HIPE_CLUSTER_GRID": "1"},
+                {"HIPE_CLUSTER_LEAD": "100000", "HIPE_CLUSTER_RSLOTS": str(plan[1] - 2)},
                 {"HIPE_CLUSTER_GRID": "1"}, {"HIPE_CLUSTER_GRID": "2"}, {"HIPE_CLUSTER_SLOTS": "7"}, {"HIPE_CLUSTER_POL1": "0"},
                 {"HIPE_CLUSTER_STASYNC": "0"}):
         os.environ.update(env)
