@@ -695,11 +695,11 @@ def run_ours(a):
             "scaling": "weak", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic", "config": cfg,
             "details": {"l2": main["l2"], "launch_plan": main["launch_plan"],
                         "algorithmic_bytes_per_volume": main["algorithmic_bytes_per_volume"],
-                        "exchange": ("hipe_peer_publish + hipe_peer_collect over NVLink peer memory (collect deferred on a side stream)" if main["exchange"] == "peer"
+                        "exchange": ("hipe_peer_publish + hipe_peer_collect over NVLink peer memory (both deferred on a side stream)" if main["exchange"] == "peer"
                                      else "NCCL all-gather of the packed records") if world > 1 else None,
                         "timing": "median of %d blocks of %d steps, each block bracketed by barrier + synchronize" % (a.blocks, a.steps),
-                        "kernels_note": ("peer_publish runs on the loss kernels' stream; peer_collect on a side stream, one step "
-                                         "deferred: its event time is mostly the wait for the slowest rank and is off the critical path")
+                        "kernels_note": ("peer_publish and peer_collect run on a side stream behind the step's loss kernel, up to two steps "
+                                         "deferred: the collect's event time is mostly the wait for the slowest rank and is off the critical path")
                         if world > 1 else None},
             "step_hbm_GBs": main["step_hbm_GBs"], "step_frac_of_peak": main["step_frac_of_peak"],
             "roofline": main["roofline"], "kernels": {k: {"ms": v} for k, v in main["kernels_ms"].items()},
