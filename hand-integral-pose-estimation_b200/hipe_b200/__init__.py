@@ -7,6 +7,6 @@ mqadri9/hand-integral-pose-estimation, behind the reference's own operator names
 """
 from . import _lib  # noqa: F401
 from ._lib import HipeError, load, lib_path  # noqa: F401
-from .graphed import GraphedCriterion, graphed  # noqa: F401
+from .graphed import GraphedCriterion, GraphedShardedStep, graphed, graphed_sharded  # noqa: F401
 
-__all__ = ["HipeError", "load", "lib_path", "graphed", "GraphedCriterion"]
+__all__ = ["HipeError", "load", "lib_path", "graphed", "GraphedCriterion", "graphed_sharded", "GraphedShardedStep"]

@@ -247,11 +247,13 @@ class _PeerExchange:
             torch.cuda.current_stream(device).wait_event(self.last_col)
             self.last_col = None
 
-    def run_deferred(self, loss_scalar, in_scale, coords, value_scale, out_dtype=torch.float64, into=None):
+    def run_deferred(self, loss_scalar, in_scale, coords, value_scale, out_dtype=torch.float64, into=None, pub_done=None):
         """-> (value 0-dim `out_dtype`, coords_all (world*b, k) fp64, event).  The two tensors are
         written on the side stream; `event` fires when they are complete.  `into`: a 0-dim fp64 tensor
         that receives the value (the unwritten loss scalar of the single-launch autograd function),
-        else a fresh one.  coords_all is one of four ring buffers: valid until four steps later."""
+        else a fresh one.  coords_all is one of four ring buffers: valid until four steps later.
+        `pub_done`: an event to record once the publish launch has read `loss_scalar` and `coords` (for
+        callers that overwrite those buffers in place, like the graphed step)."""
         from . import _lib, ops
         lib = self._lib
         dev = coords.device
@@ -284,6 +286,8 @@ class _PeerExchange:
             if timed:
                 p1.record(side)
                 ops.KERNEL_EVENTS.setdefault("peer_publish", []).append((p0, p1))
+            if pub_done is not None:
+                pub_done.record(side)
         else:
             # publish in stream order behind the loss kernels (HIPE_PUBLISH_STREAM=main); flow control:
             # publish(t) only after this rank's collect(t-1)
@@ -294,6 +298,8 @@ class _PeerExchange:
                     loss_scalar.data_ptr(), loss_scalar.numel(), float(in_scale), coords.data_ptr(), self.b, self.k,
                     self.peers_dev, self.world, self.rank, self.seq, main.cuda_stream))
             ev_pub.record(main)
+            if pub_done is not None:
+                pub_done.record(main)
             # the value's storage must outlive the side-stream write even if the caller drops the loss at
             # once: at most two collects are outstanding (flow control above), four are kept
             self.keep[i] = value

@@ -106,3 +106,72 @@ def test_sharded_criterion_nccl_world2(tmp_path, geom):
     X, Y = synth.procrustes_pairs(101, seed=4)
     rpa, rraw = P.pa_mpjpe(X, Y)
     assert abs(outs[0]["pa"] - rpa) < 1e-9 and abs(outs[1]["raw"] - rraw) < 1e-9
+
+
+def _worker_graphed(rank, world, port, B, out_dir, geom):
+    import torch.distributed as dist
+    import hipe_b200
+    from hipe_b200 import parallel as PL
+    from tests import synth
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        D, H, W = geom
+        lo, hi = PL.shard_bounds(B, world, rank)
+        batches = []
+        for seed in (42, 43, 44, 45, 46):
+            hm = synth.heatmaps(B, J, D, H, W, "peaked", seed=seed)
+            gt, vis = synth.targets(B, J, seed=seed, zero_vis_frac=0.1)
+            batches.append((torch.as_tensor(hm[lo:hi]).cuda(), torch.as_tensor(gt[lo:hi]).cuda(), torch.as_tensor(vis[lo:hi]).cuda()))
+        # eager sharded criterion: the reference of this test
+        crit = PL.ShardedJointLocationLoss(global_batch=B)
+        want = []
+        for x, g, v in batches:
+            xr = x.clone().requires_grad_(True)
+            loss = crit(xr, g, v)
+            loss.backward()
+            want.append((loss.item(), xr.grad.clone(), crit.coords.clone()))
+        # the graphed step, back to back without reading anything in between (replays run ahead of the
+        # side stream), results read afterwards from the per-step copies
+        step = hipe_b200.graphed_sharded(batches[0][0], batches[0][1], batches[0][2], global_batch=B)
+        got = []
+        for i, (x, g, v) in enumerate(batches):
+            loss, grad = step(x, g, v)
+            got.append([loss, grad.clone(), step.coords.clone()])
+            if i == 3:
+                # a loss value lives in a ring of four buffers: read the first four before the fifth step
+                for rec in got:
+                    rec[0] = (type(rec[0]).__name__, rec[0].item())
+        got[4][0] = (type(got[4][0]).__name__, got[4][0].item())
+        step.check()
+        ok = True
+        msgs = []
+        for i, ((wl, wg, wc), (l, g_, c)) in enumerate(zip(want, got)):
+            if l[0] != "DeferredLoss":
+                ok = False; msgs.append("step %d: loss is a %s" % (i, l[0]))
+            if l[1] != wl:
+                ok = False; msgs.append("step %d: loss %r != %r" % (i, l[1], wl))
+            if not torch.equal(g_, wg):
+                ok = False; msgs.append("step %d: gradient differs by %g" % (i, (g_ - wg).abs().max().item()))
+            if not torch.equal(c, wc):
+                ok = False; msgs.append("step %d: joints differ" % i)
+        np.savez(os.path.join(out_dir, "g%d.npz" % rank), ok=np.array(ok), msgs=np.array("; ".join(msgs)),
+                 losses=np.array([w[0] for w in want]))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_graphed_sharded_step_matches_eager_world2(tmp_path):
+    """hipe_b200.graphed_sharded: local launch replayed from a CUDA graph, exchange launches outside it --
+    same loss bits, gradient and gathered joints as the eager sharded criterion, five steps in a row."""
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    B, world = 6, 2
+    mp.spawn(_worker_graphed, args=(world, port, B, str(tmp_path), (32, 64, 64)), nprocs=world, join=True)
+    outs = [np.load(os.path.join(str(tmp_path), "g%d.npz" % r)) for r in range(world)]
+    for o in outs:
+        assert bool(o["ok"]), str(o["msgs"])
+    np.testing.assert_array_equal(outs[0]["losses"], outs[1]["losses"])
+    assert len(set(outs[0]["losses"].tolist())) == 5          # five different batches went through
