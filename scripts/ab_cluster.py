@@ -1,6 +1,6 @@
 """Same-box A/B of the single-launch loss+gradient kernels (CUDA events, rotating inputs larger
 than L2): cluster-resident vs persistent L2-window (resident) vs streaming fused vs the pair.
-    python scripts/ab_cluster.py [quick]"""
+    python scripts/ab_cluster.py [quick | 56 | str | 96 | lead [lead2] | pf | bfc | peek | sym | wt2]"""
 import json
 import os
 import sys
@@ -125,6 +125,23 @@ if __name__ == "__main__":
             sys.exit(0)
         case(f32, 64, 64, [{}, st(8, 20), st(8, 22), st(8, 23), {}, st(6, 18), st(6, 19), st(6, 21), st(6, 22), {}, st(6, 20, 7), st(6, 20, 9),
                            st(5, 21), st(5, 23), st(8, 21, 7), {}], False)
+        sys.exit(0)
+    if "pf" in sys.argv:
+        # resident form: L2 bulk prefetch of the stages the producer cannot load yet (HIPE_CLUSTER_PF stages ahead;
+        # 0 = off, the library's default is 4 for fp32 56^3 and single-CTA bf16 plans)
+        P, S0 = "HIPE_CLUSTER_PF", {"HIPE_CLUSTER_STREAM": "0"}
+        case(bf, 64, 128, [{P: "0"}, {P: "2"}, {P: "4"}, {P: "8"}, {P: "0"}], False)
+        case(bf, 64, 512, [{P: "0"}, {P: "4"}, {P: "0"}], False)
+        case(f32, 56, 32, [{P: "0"}, {P: "2"}, {P: "4"}, {P: "8"}, {P: "0"}], False)
+        case(f32, 32, 256, [{P: "0"}, {P: "2"}, {P: "4"}, {P: "0"}], False)
+        case(f32, 64, 64, [{}, dict(S0, **{P: "0"}), dict(S0, **{P: "4"}), dict(S0, **{P: "8"}), {}], False)
+        case(bf, 32, 256, [{P: "0"}, {P: "2"}, {P: "4"}, {P: "0"}], False)
+        sys.exit(0)
+    if "bfc" in sys.argv:
+        # bf16 64^3: cluster sizes of the resident form
+        C = "HIPE_CLUSTER_C"
+        case(bf, 64, 128, [{}, {C: "6"}, {C: "8"}, {}, {C: "5"}, {C: "3"}, {}], False)
+        case(bf, 64, 512, [{}, {C: "6"}, {C: "8"}, {}], False)
         sys.exit(0)
     if "peek" in sys.argv:
         S8 = {"HIPE_CLUSTER_STREAM": "1", "HIPE_CLUSTER_C": "8"}
