@@ -104,3 +104,42 @@ def test_launch_plan_host_logic():
     lib = __import__("hipe_b200._lib", fromlist=["load"]).load()
     assert lib.hipe_resident_workspace_bytes(0, 1344, 64, 64, 64) > 0
     assert lib.hipe_resident_workspace_bytes(0, 1344, 5, 6, 7) == 0
+
+
+def test_cluster_plan_invariants_over_a_sweep_of_geometries():
+    """hipe_cluster_plan is host-only arithmetic: for every geometry it accepts, the plan must be one
+    the kernel's pipeline logic is safe on -- shares cover the volume, the ring holds a share with
+    look-ahead (resident form) or the lead exceeds the share (streamed form: the no-cycle condition
+    of the first producer's throttle), 16-CTA clusters only where the kernel has 16 exchange slots."""
+    import torch
+    from hipe_b200 import ops
+    seen = {"resident": 0, "streamed": 0, "none": 0}
+    for dt in (torch.float32, torch.bfloat16):
+        esz = 4 if dt == torch.float32 else 2
+        x = torch.empty(0, dtype=dt)
+        for D, H, W in [(d, d, d) for d in (8, 16, 24, 32, 40, 48, 56, 64, 72, 80, 96, 112, 128)] + \
+                       [(16, 128, 64), (12, 20, 24), (32, 96, 96), (64, 32, 32), (5, 6, 7), (3, 9, 100), (96, 96, 64)]:
+            plan = ops.cluster_plan(x, 1344, D, H, W)
+            if plan is None:
+                seen["none"] += 1
+                continue
+            C, slots, share, stage_bytes, lead = plan
+            row_bytes = W * esz
+            assert row_bytes % 16 == 0 and stage_bytes % row_bytes == 0 and 0 < stage_bytes <= 16384, (dt, D, H, W, plan)
+            nsv = D * H * W * esz // stage_bytes
+            assert nsv * stage_bytes == D * H * W * esz                     # whole stages
+            assert 1 <= C <= 16 and share == -(-nsv // C) and nsv >= C, (dt, D, H, W, plan)
+            assert slots * stage_bytes <= 227 * 1024
+            if lead == 0:
+                seen["resident"] += 1
+                assert C <= 8 and share + 3 <= slots, (dt, D, H, W, plan)
+            else:
+                seen["streamed"] += 1
+                assert lead > share and slots >= 6, (dt, D, H, W, plan)
+                if C > 8:
+                    assert C == 16 and dt == torch.float32 and row_bytes == 384, (dt, D, H, W, plan)
+            # what the module would launch: the cluster plan only where the L2 bound of the streamed form holds
+            if ops._fused_plan(torch.empty(1, dtype=dt), 1344, D, H, W) == "cluster" and lead > 0:
+                sms = {8: 120, 16: 112}.get(C, 148)
+                assert lead * stage_bytes * sms <= 46e6, (dt, D, H, W, plan)
+    assert seen["resident"] >= 8 and seen["streamed"] >= 4 and seen["none"] >= 2, seen
